@@ -1,0 +1,10 @@
+"""b200_train — B200-native drop-in for the data-parallel training-step tail of ericehanley/gke-ray-train.
+
+Host code is Python/PyTorch (device memory, streams, torch.distributed bootstrap); all arithmetic on the path
+runs in hand-written sm_100a kernels behind the C ABI in include/b2train.h (libb2train.so). There is no CPU
+fallback: importing this package without the built library fails.
+"""
+from . import _lib, ops  # noqa: F401
+from ._lib import B2Error  # noqa: F401
+
+__version__ = "0.1.0"

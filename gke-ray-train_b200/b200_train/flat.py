@@ -1,0 +1,116 @@
+"""Flat parameter / gradient storage.
+
+The fused kernels (gradient sum-of-squares, AdamW, peer-memory all-reduce) run over one contiguous buffer per
+dtype instead of one launch per parameter. `flatten_params` re-homes every parameter's storage into such a
+buffer (the parameter objects stay the same, so `model.parameters()`, `state_dict()` and autograd are
+unaffected) and installs `.grad` tensors that are views of a matching flat gradient buffer — the arrangement
+DistributedDataParallel calls `gradient_as_bucket_view` ($SP/torch/nn/parallel/distributed.py:655), which
+prepare_model installs for the reference (ref: ray-jobs/pytorch_llm_ray.py:230).
+"""
+import torch
+
+ALIGN = 64  # elements; every parameter starts on a 64-element boundary (>= 128 B), padding stays zero
+
+
+class FlatBuffer:
+    """One dtype's worth of parameters laid out back to back."""
+
+    def __init__(self, dtype, device, params, alloc=None):
+        self.dtype, self.device = dtype, device
+        self.params = list(params)
+        self.offsets = []
+        off = 0
+        for p in self.params:
+            self.offsets.append(off)
+            off += (p.numel() + ALIGN - 1) // ALIGN * ALIGN
+        self.numel = off
+        alloc = alloc or (lambda n, dt, dev: torch.zeros(n, dtype=dt, device=dev))
+        self.data = alloc(self.numel, dtype, device)
+        self.grad = alloc(self.numel, dtype, device)
+        self.data.zero_()
+        self.grad.zero_()
+        with torch.no_grad():
+            for p, o in zip(self.params, self.offsets):
+                view = self.data[o:o + p.numel()].view(p.shape)
+                view.copy_(p.data)
+                p.data = view
+                p._b2_flat = (self, o)
+        self.install_grads()
+        # set by clip_grad_norm_ when an attached optimizer will apply the coefficient inside its kernel
+        self.pending_coef = None
+        self.optimizer_attached = False
+        # exp_avg / exp_avg_sq, created by the optimizer
+        self.exp_avg = None
+        self.exp_avg_sq = None
+
+    def grad_view(self, i):
+        p, o = self.params[i], self.offsets[i]
+        return self.grad[o:o + p.numel()].view(p.shape)
+
+    def install_grads(self):
+        """(Re-)point every parameter's .grad at its slice of the flat gradient buffer. A .grad that autograd
+        allocated on its own since (after a zero_grad(set_to_none=True) issued elsewhere) is copied in first."""
+        moved = 0
+        for i, p in enumerate(self.params):
+            want = self.grad_view(i)
+            g = p.grad
+            if g is None:
+                p.grad = want
+            elif g.data_ptr() != want.data_ptr():
+                want.copy_(g)
+                p.grad = want
+                moved += 1
+        return moved
+
+    def zero_grad(self):
+        self.grad.zero_()
+        self.pending_coef = None
+
+
+def flat_of(p):
+    return getattr(p, "_b2_flat", None)
+
+
+def flatten_params(params, alloc=None):
+    """Flattens the given parameters (those not already flattened) by (device, dtype). Returns the list of
+    FlatBuffers that now hold them, in first-appearance order."""
+    seen, groups, order = set(), {}, []
+    existing = []
+    for p in params:
+        if id(p) in seen:
+            continue
+        seen.add(id(p))
+        if not p.requires_grad:
+            continue
+        f = flat_of(p)
+        if f is not None:
+            if f[0] not in existing:
+                existing.append(f[0])
+            continue
+        if not p.is_cuda:
+            raise RuntimeError("b200_train: parameters must be on a CUDA device before they are flattened "
+                               "(there is no CPU path)")
+        key = (p.device, p.dtype)
+        if key not in groups:
+            groups[key] = []
+            order.append(key)
+        groups[key].append(p)
+    out = list(existing)
+    for key in order:
+        out.append(FlatBuffer(key[1], key[0], groups[key], alloc=alloc))
+    return out
+
+
+def buffers_of(params):
+    """Distinct FlatBuffers behind `params`, plus the parameters that are not flattened."""
+    bufs, loose, seen = [], [], set()
+    for p in params:
+        if id(p) in seen:
+            continue
+        seen.add(id(p))
+        f = flat_of(p)
+        if f is None:
+            loose.append(p)
+        elif f[0] not in bufs:
+            bufs.append(f[0])
+    return bufs, loose

@@ -1,0 +1,190 @@
+"""Tensor-level wrappers over the C ABI (include/b2train.h). PyTorch is used for device memory and
+streams only; every function here enqueues hand-written sm_100a kernels and nothing else.
+"""
+import torch
+
+from . import _lib
+from ._lib import B2Error, call, dtype_code, ptr, require_cuda, stream_ptr
+
+_scratch = {}
+
+
+def _sumsq_scratch(device):
+    """Zero-initialised scratch for b2_sumsq, one per (device, stream) so overlapping calls never share it."""
+    key = (device.index, torch.cuda.current_stream(device).cuda_stream)
+    buf = _scratch.get(key)
+    if buf is None:
+        buf = torch.zeros(_lib.lib.b2_sumsq_scratch_bytes() // 4, dtype=torch.float32, device=device)
+        _scratch[key] = buf
+    return buf
+
+
+def _flat(t, what):
+    if not t.is_contiguous():
+        raise B2Error(f"{what} must be contiguous")
+    return t
+
+
+def adamw_(p, g, m, v, *, lr, beta1=0.9, beta2=0.999, eps=1e-8, weight_decay=1e-2, step, gscale=None):
+    """In-place fused AdamW on flat (contiguous) tensors. `step` is the 1-based step count."""
+    require_cuda(p, g, m, v, gscale)
+    n = p.numel()
+    if not (g.numel() == n and m.numel() == n and v.numel() == n):
+        raise B2Error("adamw_: p, g, m, v must have the same number of elements")
+    if m.dtype != v.dtype:
+        raise B2Error("adamw_: exp_avg and exp_avg_sq must share a dtype")
+    for t, w in ((p, "p"), (g, "g"), (m, "m"), (v, "v")):
+        _flat(t, w)
+    with torch.cuda.device(p.device):
+        call("b2_adamw", ptr(p), ptr(g), ptr(m), ptr(v), n, dtype_code(p.dtype), dtype_code(g.dtype),
+             dtype_code(m.dtype), float(lr), float(beta1), float(beta2), float(eps), float(weight_decay), int(step),
+             ptr(gscale), stream_ptr())
+
+
+def sumsq(g, out=None, accumulate=False):
+    """Sum of squares of a flat tensor -> 1-element fp32 device tensor (no host sync)."""
+    require_cuda(g)
+    _flat(g, "g")
+    if out is None:
+        out = torch.empty(1, dtype=torch.float32, device=g.device)
+        accumulate = False
+    with torch.cuda.device(g.device):
+        call("b2_sumsq", ptr(g), g.numel(), dtype_code(g.dtype), ptr(_sumsq_scratch(g.device)), ptr(out),
+             int(bool(accumulate)), stream_ptr())
+    return out
+
+
+def clip_coef(sumsq_parts, max_norm):
+    """(total_norm, coef) device scalars from a fp32 vector of sum-of-squares partials."""
+    require_cuda(sumsq_parts)
+    if sumsq_parts.dtype != torch.float32:
+        raise B2Error("clip_coef: partials must be float32")
+    norm = torch.empty(1, dtype=torch.float32, device=sumsq_parts.device)
+    coef = torch.empty(1, dtype=torch.float32, device=sumsq_parts.device)
+    with torch.cuda.device(sumsq_parts.device):
+        call("b2_clip_coef", ptr(sumsq_parts), sumsq_parts.numel(), float(max_norm), ptr(norm), ptr(coef), stream_ptr())
+    return norm, coef
+
+
+def scale_(g, coef):
+    require_cuda(g, coef)
+    _flat(g, "g")
+    with torch.cuda.device(g.device):
+        call("b2_scale", ptr(g), g.numel(), dtype_code(g.dtype), ptr(coef), stream_ptr())
+    return g
+
+
+class CEResult:
+    """Device-side results of a cross-entropy forward: nothing here forces a host sync."""
+    __slots__ = ("lse", "zt", "loss", "n_valid", "err")
+
+    def __init__(self, lse, zt, loss, n_valid, err):
+        self.lse, self.zt, self.loss, self.n_valid, self.err = lse, zt, loss, n_valid, err
+
+    @property
+    def loss_sum(self):
+        return self.loss[0]
+
+    @property
+    def loss_mean(self):
+        return self.loss[1]
+
+
+def _ce_outputs(N, device):
+    lse = torch.empty(max(N, 1), dtype=torch.float32, device=device)
+    zt = torch.zeros(max(N, 1), dtype=torch.float32, device=device)
+    loss = torch.empty(2, dtype=torch.float32, device=device)
+    n_valid = torch.empty(1, dtype=torch.int64, device=device)
+    err = torch.empty(1, dtype=torch.int32, device=device)
+    return lse, zt, loss, n_valid, err
+
+
+def _check_labels(labels, N):
+    if labels.dtype != torch.int64:
+        raise B2Error("labels must be int64")
+    if labels.numel() != N:
+        raise B2Error(f"labels has {labels.numel()} elements, expected {N}")
+    return _flat(labels, "labels")
+
+
+def ce_rows_fwd(logits, labels, shift_T=0, ignore_index=-100):
+    """Cross-entropy over materialised logits [N, V] (row stride may exceed V)."""
+    require_cuda(logits, labels)
+    if logits.dim() != 2 or logits.stride(1) != 1:
+        raise B2Error("ce_rows_fwd: logits must be [N, V] with unit column stride")
+    N, V = logits.shape
+    ld = logits.stride(0) if N > 1 else max(V, logits.stride(0))
+    _check_labels(labels, N)
+    lse, zt, loss, n_valid, err = _ce_outputs(N, logits.device)
+    with torch.cuda.device(logits.device):
+        call("b2_ce_rows_fwd", ptr(logits), dtype_code(logits.dtype), N, V, ld, ptr(labels), int(shift_T),
+             int(ignore_index), ptr(lse), ptr(zt), ptr(loss), ptr(n_valid), ptr(err), stream_ptr())
+    return CEResult(lse, zt, loss, n_valid, err)
+
+
+def ce_rows_bwd(logits, labels, lse, gscale, shift_T=0, ignore_index=-100, out=None):
+    require_cuda(logits, labels, lse, gscale)
+    N, V = logits.shape
+    ld = logits.stride(0) if N > 1 else max(V, logits.stride(0))
+    if out is None:
+        out = torch.empty_strided(logits.shape, logits.stride(), dtype=logits.dtype, device=logits.device)
+    elif out.stride() != logits.stride() or out.dtype != logits.dtype:
+        raise B2Error("ce_rows_bwd: out must match logits' dtype and strides")
+    with torch.cuda.device(logits.device):
+        call("b2_ce_rows_bwd", ptr(logits), dtype_code(logits.dtype), N, V, ld, ptr(labels), int(shift_T),
+             int(ignore_index), ptr(lse), ptr(gscale), ptr(out), stream_ptr())
+    return out
+
+
+def _check_hw(H, W, bias):
+    require_cuda(H, W, bias)
+    if H.dtype != torch.bfloat16 or W.dtype != torch.bfloat16:
+        raise B2Error("the fused LM-head kernel takes bfloat16 hidden states and weight")
+    if H.dim() != 2 or W.dim() != 2 or H.stride(1) != 1 or W.stride(1) != 1 or H.shape[1] != W.shape[1]:
+        raise B2Error("expected H [N, D] and W [V, D] with unit inner stride")
+    if bias is not None and (bias.dtype != torch.float32 or bias.numel() != W.shape[0] or not bias.is_contiguous()):
+        raise B2Error("bias must be a contiguous float32 [V] tensor")
+
+
+def lmhead_ce_fwd(H, W, labels, bias=None, shift_T=0, ignore_index=-100, round_logits_bf16=True):
+    """Fused logits = H @ W.T (+bias) and cross-entropy; logits are never materialised."""
+    _check_hw(H, W, bias)
+    N, D = H.shape
+    V = W.shape[0]
+    _check_labels(labels, N)
+    lse, zt, loss, n_valid, err = _ce_outputs(N, H.device)
+    with torch.cuda.device(H.device):
+        ws_bytes = _lib.lib.b2_lmhead_ce_workspace_bytes(N)
+        ws = torch.empty(max(ws_bytes, 16), dtype=torch.uint8, device=H.device)
+        call("b2_lmhead_ce_fwd", ptr(H), H.stride(0), ptr(W), W.stride(0), ptr(bias), ptr(labels), N, D, V,
+             int(shift_T), int(ignore_index), int(bool(round_logits_bf16)), ptr(ws), ws_bytes, ptr(lse), ptr(zt),
+             ptr(loss), ptr(n_valid), ptr(err), stream_ptr())
+    return CEResult(lse, zt, loss, n_valid, err)
+
+
+def lmhead_ce_bwd_dlogits(H, W, labels, lse, gscale, row0, rows, out, bias=None, shift_T=0, ignore_index=-100,
+                          round_logits_bf16=True):
+    """d(logits) for rows [row0, row0+rows) into `out` (bf16 [>=rows, ldd])."""
+    _check_hw(H, W, bias)
+    if out.dtype != torch.bfloat16 or out.stride(1) != 1:
+        raise B2Error("dlogits buffer must be bfloat16 with unit inner stride")
+    D, V = H.shape[1], W.shape[0]
+    Hc = H[row0:row0 + rows]
+    with torch.cuda.device(H.device):
+        call("b2_lmhead_ce_bwd_dlogits", ptr(Hc), H.stride(0), ptr(W), W.stride(0), ptr(bias), ptr(labels), int(row0),
+             int(rows), D, V, int(shift_T), int(ignore_index), int(bool(round_logits_bf16)), ptr(lse), ptr(gscale),
+             ptr(out), out.stride(0), stream_ptr())
+    return out
+
+
+def gemm_bf16(A, B, C, M, N, K, a_mn_major=False, b_mn_major=False, accumulate=False):
+    """C[M,N] (+)= A[M,K] @ B[N,K]^T. A is stored [M, lda] (K-major) or [K, lda] (MN-major); same for B."""
+    require_cuda(A, B, C)
+    if A.dtype != torch.bfloat16 or B.dtype != torch.bfloat16:
+        raise B2Error("gemm_bf16: A and B must be bfloat16")
+    if A.stride(1) != 1 or B.stride(1) != 1 or C.stride(1) != 1:
+        raise B2Error("gemm_bf16: unit inner stride required")
+    with torch.cuda.device(A.device):
+        call("b2_gemm_bf16", ptr(A), int(a_mn_major), A.stride(0), ptr(B), int(b_mn_major), B.stride(0), ptr(C),
+             dtype_code(C.dtype), C.stride(0), int(M), int(N), int(K), int(bool(accumulate)), stream_ptr())
+    return C

@@ -1,0 +1,510 @@
+// F1 — LM head fused with causal cross-entropy on the 5th-gen tensor cores (tcgen05 + TMEM + TMA).
+//
+// Replaces, for bf16 models, the pair the reference executes at the end of every forward:
+//   logits = lm_head(hidden)                  (transformers/models/llama/modeling_llama.py:486-491,
+//                                              reached from trainer.train(), ref: ray-jobs/fine_tune_llama_ray.py:333;
+//                                              BasicLLM.fc_out, ref: ray-jobs/pytorch_llm_ray.py:87,104)
+//   loss   = ForCausalLMLoss(logits, labels)  (transformers/loss/loss_utils.py:45-67: .float(), shift, CE with
+//                                              ignore_index=-100; nn.CrossEntropyLoss at ref: pytorch_llm_ray.py:237,275)
+// The [tokens x vocab] logits are never written to memory: each 128x256 logits tile lives in TMEM, and
+// the epilogue warps fold it into a per-row running (max, sum-exp) and pick out the label's logit.
+// Backward recomputes the tile and writes d(logits) for a bounded chunk of rows only (bf16), which two
+// plain GEMMs (same mainloop, MODE_GEMM) turn into dH and dW.
+//
+// One kernel template, three epilogues:
+//   MODE_GEMM    C[M,N] (+)= A[M,K] * B[N,K]^T          (A/B each K-major or MN-major in memory)
+//   MODE_CE_FWD  per (row, vocab split): (max, sumexp) partials + label logit
+//   MODE_CE_BWD  dlogits[row, col] = (exp(logit - lse[row]) - [col == label]) * gscale   (0 for ignored rows)
+//
+// Tile 128 (M) x 256 (N) x 64 (K), tcgen05.mma cta_group::1 kind::f16 M=128 N=256 K=16, fp32 accumulators
+// double-buffered in TMEM (2 x 256 columns) so the epilogue of tile i overlaps the MMAs of tile i+1.
+// Warp roles (256 threads, 1 CTA/SM, persistent over work units): warp 0 = TMA producer, warp 1 = MMA issuer,
+// warp 2 = TMEM allocator, warps 4-7 = epilogue (one TMEM lane = one row per thread).
+// Tensor-bound: algorithmic flops = 2*M*N*K per pass.
+#include "b2_common.cuh"
+#include "umma.cuh"
+#include <math.h>
+#include <mutex>
+
+int b2_ce_finalize_launch(const float* lse, const float* zt, const long long* labels, long long N, long long V,
+                          int shift_T, long long ignore_index, float* loss_out, long long* n_valid_out, int* err_out,
+                          cudaStream_t stream);
+
+namespace {
+
+using namespace umma;
+
+constexpr int BM = 128, BN = 256, BK = 64, STAGES = 4, UK = 16;
+constexpr int A_STAGE_BYTES = BM * BK * 2;            // 16 KiB
+constexpr int B_STAGE_BYTES = BN * BK * 2;            // 32 KiB
+constexpr int STAGE_BYTES = A_STAGE_BYTES + B_STAGE_BYTES;
+constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024;   // + slack to reach 1024-byte alignment
+constexpr int BOX_MN_BYTES = 64 * BK * 2;             // one MN-major TMA box: 64 K-rows x 128 B
+constexpr uint32_t TMEM_COLS = 512;
+constexpr int MAX_SPLITS = 64;
+constexpr float LOG2E = 1.4426950408889634f;
+
+enum { MODE_GEMM = 0, MODE_CE_FWD = 1, MODE_CE_BWD = 2 };
+
+struct Params {
+  int M, N, K;                       // rows (tokens), columns (vocab or features), reduction extent
+  int num_m_blocks, num_n_blocks, num_k_blocks, n_splits;
+  // MODE_GEMM
+  void* C; long long ldc; int c_dtype; int accumulate;
+  // cross-entropy modes
+  const long long* labels; int shift_T; long long ignore_index; long long row0;
+  const float* bias; int round_bf16;
+  float2* part; long long part_stride; float* zt;
+  const float* lse; const float* gscale; __nv_bfloat16* dlogits; long long ldd;
+};
+
+__device__ __forceinline__ float fast_exp2(float x) {
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+
+__device__ __forceinline__ long long label_at(const Params& p, long long i) {
+  if (p.shift_T <= 0) return p.labels[i];
+  return ((i % p.shift_T) + 1 < p.shift_T) ? p.labels[i + 1] : p.ignore_index;
+}
+
+template <int MODE, int A_MN, int B_MN>
+__global__ void __launch_bounds__(256, 1)
+umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const Params p) {
+  extern __shared__ uint8_t smem_raw[];
+  __shared__ uint64_t full_bar[STAGES], empty_bar[STAGES], tfull_bar[2], tempty_bar[2];
+  __shared__ uint32_t tmem_holder;
+
+  uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+
+  if (threadIdx.x == 0) { tma_prefetch_desc(&tmA); tma_prefetch_desc(&tmB); }
+  if (threadIdx.x == 32) {
+    for (int i = 0; i < STAGES; ++i) { mbar_init(&full_bar[i], 1); mbar_init(&empty_bar[i], 1); }
+    for (int i = 0; i < 2; ++i) { mbar_init(&tfull_bar[i], 1); mbar_init(&tempty_bar[i], 128); }
+    fence_mbar_init();
+  }
+  if (warp == 2) tmem_alloc<TMEM_COLS>(&tmem_holder);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = tmem_holder;
+
+  const int num_units = p.num_m_blocks * p.n_splits;
+
+  if (warp == 0) {
+    // ------------------------------------------------------------ TMA producer
+    if (lane == 0) {
+      int stage = 0; uint32_t phase = 0;
+      for (int u = blockIdx.x; u < num_units; u += gridDim.x) {
+        const int mb = u % p.num_m_blocks, s = u / p.num_m_blocks;
+        const int nb0 = (int)((long long)s * p.num_n_blocks / p.n_splits);
+        const int nb1 = (int)((long long)(s + 1) * p.num_n_blocks / p.n_splits);
+        for (int nb = nb0; nb < nb1; ++nb) {
+          for (int kb = 0; kb < p.num_k_blocks; ++kb) {
+            mbar_wait(&empty_bar[stage], phase ^ 1);
+            mbar_arrive_expect_tx(&full_bar[stage], STAGE_BYTES);
+            uint8_t* sa = smem + stage * STAGE_BYTES;
+            uint8_t* sb = sa + A_STAGE_BYTES;
+            if (!A_MN) tma_load_2d(sa, &tmA, &full_bar[stage], kb * BK, mb * BM);
+            else {
+#pragma unroll
+              for (int j = 0; j < BM / 64; ++j) tma_load_2d(sa + j * BOX_MN_BYTES, &tmA, &full_bar[stage], mb * BM + j * 64, kb * BK);
+            }
+            if (!B_MN) tma_load_2d(sb, &tmB, &full_bar[stage], kb * BK, nb * BN);
+            else {
+#pragma unroll
+              for (int j = 0; j < BN / 64; ++j) tma_load_2d(sb + j * BOX_MN_BYTES, &tmB, &full_bar[stage], nb * BN + j * 64, kb * BK);
+            }
+            if (++stage == STAGES) { stage = 0; phase ^= 1; }
+          }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ------------------------------------------------------------ MMA issuer (one thread)
+    if (lane == 0) {
+      constexpr uint32_t idesc = make_idesc_bf16(BM, BN, A_MN, B_MN);
+      int stage = 0; uint32_t phase = 0;
+      int as = 0; uint32_t aphase = 0;
+      for (int u = blockIdx.x; u < num_units; u += gridDim.x) {
+        const int s = u / p.num_m_blocks;
+        const int nb0 = (int)((long long)s * p.num_n_blocks / p.n_splits);
+        const int nb1 = (int)((long long)(s + 1) * p.num_n_blocks / p.n_splits);
+        for (int nb = nb0; nb < nb1; ++nb) {
+          mbar_wait(&tempty_bar[as], aphase ^ 1);
+          tc_fence_after();
+          const uint32_t tmem_d = tmem_base + (uint32_t)(as * BN);
+          for (int kb = 0; kb < p.num_k_blocks; ++kb) {
+            mbar_wait(&full_bar[stage], phase);
+            tc_fence_after();
+            const uint32_t a_addr = smem_u32(smem + stage * STAGE_BYTES);
+            const uint32_t b_addr = a_addr + A_STAGE_BYTES;
+#pragma unroll
+            for (int k = 0; k < BK / UK; ++k) {
+              const uint64_t adesc = A_MN ? make_sdesc_sw128(a_addr + k * (UK * 128), BOX_MN_BYTES, 1024)
+                                          : make_sdesc_sw128(a_addr + k * (UK * 2), 16, 1024);
+              const uint64_t bdesc = B_MN ? make_sdesc_sw128(b_addr + k * (UK * 128), BOX_MN_BYTES, 1024)
+                                          : make_sdesc_sw128(b_addr + k * (UK * 2), 16, 1024);
+              mma_bf16_ss(tmem_d, adesc, bdesc, idesc, (uint32_t)((kb | k) != 0));
+            }
+            mma_commit(&empty_bar[stage]);          // frees the smem slot once these MMAs retire
+            if (++stage == STAGES) { stage = 0; phase ^= 1; }
+          }
+          mma_commit(&tfull_bar[as]);               // accumulator tile complete
+          as ^= 1; if (as == 0) aphase ^= 1;
+        }
+      }
+    }
+  } else if (warp >= 4) {
+    // ------------------------------------------------------------ epilogue: TMEM -> registers -> result
+    const int q = warp & 3;                         // TMEM lane quarter this warp may read
+    const int trow = q * 32 + lane;                 // row inside the tile
+    int as = 0; uint32_t aphase = 0;
+    for (int u = blockIdx.x; u < num_units; u += gridDim.x) {
+      const int mb = u % p.num_m_blocks, s = u / p.num_m_blocks;
+      const int nb0 = (int)((long long)s * p.num_n_blocks / p.n_splits);
+      const int nb1 = (int)((long long)(s + 1) * p.num_n_blocks / p.n_splits);
+      const long long row = (long long)mb * BM + trow;
+      const bool row_ok = row < p.M;
+
+      // per-row state for the cross-entropy epilogues
+      float run_m = -INFINITY, run_s = 0.f, zval = 0.f;
+      long long y = -1;
+      float row_lse_l2 = 0.f, gs = 0.f;
+      if (MODE != MODE_GEMM && row_ok) {
+        y = label_at(p, p.row0 + row);
+        if (MODE == MODE_CE_BWD) {
+          const bool valid = (y != p.ignore_index) && y >= 0 && y < p.N;
+          row_lse_l2 = p.lse[p.row0 + row] * LOG2E;
+          gs = valid ? __ldg(p.gscale) : 0.f;
+          if (!valid) y = -1;
+        }
+      }
+
+      for (int nb = nb0; nb < nb1; ++nb) {
+        mbar_wait(&tfull_bar[as], aphase);
+        tc_fence_after();
+#pragma unroll 1
+        for (int c = 0; c < BN / 32; ++c) {
+          const int col0 = nb * BN + c * 32;
+          if (col0 >= p.N) break;                   // warp-uniform: nothing but padding from here on
+          uint32_t r[32];
+          tmem_ld_32x32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(as * BN + c * 32), r);
+          tmem_ld_wait();
+
+          if (MODE == MODE_GEMM) {
+            if (row_ok) {
+              const int ncol = min(32, p.N - col0);
+              if (p.c_dtype == B2_F32) {
+                float* dst = static_cast<float*>(p.C) + row * p.ldc + col0;
+                if (ncol == 32 && ((reinterpret_cast<uintptr_t>(dst) & 15) == 0)) {
+#pragma unroll
+                  for (int j = 0; j < 32; j += 4) {
+                    float4 v = make_float4(__uint_as_float(r[j]), __uint_as_float(r[j + 1]), __uint_as_float(r[j + 2]), __uint_as_float(r[j + 3]));
+                    if (p.accumulate) { const float4 o = *reinterpret_cast<const float4*>(dst + j); v.x += o.x; v.y += o.y; v.z += o.z; v.w += o.w; }
+                    *reinterpret_cast<float4*>(dst + j) = v;
+                  }
+                } else {
+#pragma unroll
+                  for (int j = 0; j < 32; ++j)
+                    if (j < ncol) dst[j] = __uint_as_float(r[j]) + (p.accumulate ? dst[j] : 0.f);
+                }
+              } else {
+                __nv_bfloat16* dst = static_cast<__nv_bfloat16*>(p.C) + row * p.ldc + col0;
+                if (ncol == 32 && ((reinterpret_cast<uintptr_t>(dst) & 15) == 0)) {
+#pragma unroll
+                  for (int j = 0; j < 32; j += 8) {
+                    float v[8];
+#pragma unroll
+                    for (int t = 0; t < 8; ++t) v[t] = __uint_as_float(r[j + t]);
+                    if (p.accumulate) {
+                      const uint4 o = *reinterpret_cast<const uint4*>(dst + j);
+                      v[0] += bf16_lo(o.x); v[1] += bf16_hi(o.x); v[2] += bf16_lo(o.y); v[3] += bf16_hi(o.y);
+                      v[4] += bf16_lo(o.z); v[5] += bf16_hi(o.z); v[6] += bf16_lo(o.w); v[7] += bf16_hi(o.w);
+                    }
+                    *reinterpret_cast<uint4*>(dst + j) = make_uint4(pack_bf16(v[0], v[1]), pack_bf16(v[2], v[3]), pack_bf16(v[4], v[5]), pack_bf16(v[6], v[7]));
+                  }
+                } else {
+#pragma unroll
+                  for (int j = 0; j < 32; ++j) {
+                    if (j < ncol) {
+                      const float o = p.accumulate ? __bfloat162float(dst[j]) : 0.f;
+                      dst[j] = __float2bfloat16_rn(__uint_as_float(r[j]) + o);
+                    }
+                  }
+                }
+              }
+            }
+          } else {
+            // logits for this row, columns [col0, col0+32)
+            float x[32];
+#pragma unroll
+            for (int j = 0; j < 32; ++j) x[j] = __uint_as_float(r[j]);
+            if (p.bias != nullptr) {
+#pragma unroll
+              for (int j = 0; j < 32; ++j) x[j] += (col0 + j < p.N) ? __ldg(p.bias + col0 + j) : 0.f;
+            }
+            if (p.round_bf16) {
+#pragma unroll
+              for (int j = 0; j < 32; ++j) x[j] = round_bf16(x[j]);
+            }
+            const bool ragged = col0 + 32 > p.N;    // last chunk of the vocabulary: mask the padding columns
+
+            if (MODE == MODE_CE_FWD) {
+              if (ragged) {
+#pragma unroll
+                for (int j = 0; j < 32; ++j) if (col0 + j >= p.N) x[j] = -INFINITY;
+              }
+              float cmax = x[0];
+#pragma unroll
+              for (int j = 1; j < 32; ++j) cmax = fmaxf(cmax, x[j]);
+              const float nm = fmaxf(run_m, cmax);
+              const float nm_l2 = nm * LOG2E;
+              float acc0 = 0.f, acc1 = 0.f;
+#pragma unroll
+              for (int j = 0; j < 32; j += 2) {
+                acc0 += fast_exp2(fmaf(x[j], LOG2E, -nm_l2));
+                acc1 += fast_exp2(fmaf(x[j + 1], LOG2E, -nm_l2));
+              }
+              run_s = run_s * fast_exp2((run_m - nm) * LOG2E) + (acc0 + acc1);
+              run_m = nm;
+              if (y >= col0 && y < col0 + 32) {
+                const int jj = (int)(y - col0);
+#pragma unroll
+                for (int j = 0; j < 32; ++j) if (j == jj) zval = x[j];
+              }
+            } else {  // MODE_CE_BWD
+              if (row_ok) {
+                const int jj = (y >= col0 && y < col0 + 32) ? (int)(y - col0) : -1;
+                float d[32];
+#pragma unroll
+                for (int j = 0; j < 32; ++j) {
+                  const float pj = fast_exp2(fmaf(x[j], LOG2E, -row_lse_l2));
+                  d[j] = (pj - (j == jj ? 1.f : 0.f)) * gs;
+                }
+                if (ragged) {
+#pragma unroll
+                  for (int j = 0; j < 32; ++j) if (col0 + j >= p.N) d[j] = 0.f;
+                }
+                __nv_bfloat16* dst = p.dlogits + row * p.ldd + col0;
+#pragma unroll
+                for (int j = 0; j < 32; j += 8) {
+                  if (col0 + j + 8 <= p.ldd)
+                    *reinterpret_cast<uint4*>(dst + j) = make_uint4(pack_bf16(d[j], d[j + 1]), pack_bf16(d[j + 2], d[j + 3]),
+                                                                    pack_bf16(d[j + 4], d[j + 5]), pack_bf16(d[j + 6], d[j + 7]));
+                }
+              }
+            }
+          }
+        }
+        tc_fence_before();
+        mbar_arrive(&tempty_bar[as]);               // 128 arrivals hand the accumulator stage back to the MMA warp
+        as ^= 1; if (as == 0) aphase ^= 1;
+      }
+
+      if (MODE == MODE_CE_FWD && row_ok) {
+        p.part[(long long)s * p.part_stride + row] = make_float2(run_m, run_s);
+        if (y >= (long long)nb0 * BN && y < (long long)nb1 * BN && y < p.N) p.zt[row] = zval;
+      }
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 2) { tc_fence_after(); tmem_dealloc<TMEM_COLS>(tmem_base); }
+}
+
+// merge the per-split (max, sumexp) partials of each row into lse[row]
+__global__ void __launch_bounds__(256) ce_combine_kernel(const float2* __restrict__ part, long long part_stride, int n_splits,
+                                                         long long N, float* __restrict__ lse) {
+  const long long row = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (row >= N) return;
+  float m = -INFINITY, s = 0.f;
+  for (int k = 0; k < n_splits; ++k) {
+    const float2 v = part[(long long)k * part_stride + row];
+    const float nm = fmaxf(m, v.x);
+    s = s * exp2f((m - nm) * LOG2E) + v.y * exp2f((v.x - nm) * LOG2E);
+    m = nm;
+  }
+  lse[row] = m + logf(s);
+}
+
+// ------------------------------------------------------------------ host side
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                  const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+EncodeTiledFn get_encode_fn() {
+  static EncodeTiledFn fn = nullptr;
+  static std::once_flag once;
+  std::call_once(once, [] {
+    void* ptr = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &ptr, cudaEnableDefault, &q) == cudaSuccess &&
+        q == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<EncodeTiledFn>(ptr);
+    else
+      cudaGetLastError();
+  });
+  return fn;
+}
+
+// bf16 2-D row-major tensor [outer, inner] with row pitch `pitch_elems`; box = box_inner x box_outer, 128B swizzle,
+// out-of-bounds elements read as zero.
+int make_tmap(CUtensorMap* m, const void* ptr, long long inner, long long outer, long long pitch_elems, int box_inner,
+              int box_outer, const char* what) {
+  EncodeTiledFn fn = get_encode_fn();
+  if (!fn) { b2_set_error("cuTensorMapEncodeTiled is not available from this driver"); return B2_ERR_CUDA; }
+  B2_REQUIRE(b2_aligned(ptr, 16), "%s: base pointer must be 16-byte aligned", what);
+  B2_REQUIRE((pitch_elems * 2) % 16 == 0, "%s: row pitch (%lld elements) must be a multiple of 8 bf16 elements", what, pitch_elems);
+  B2_REQUIRE(inner >= 1 && outer >= 1 && pitch_elems >= inner, "%s: bad extents inner=%lld outer=%lld pitch=%lld", what, inner, outer, pitch_elems);
+  cuuint64_t dims[2] = {(cuuint64_t)inner, (cuuint64_t)outer};
+  cuuint64_t strides[1] = {(cuuint64_t)pitch_elems * 2};
+  cuuint32_t box[2] = {(cuuint32_t)box_inner, (cuuint32_t)box_outer};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = fn(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(ptr), dims, strides, box, estr,
+                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) { b2_set_error("%s: cuTensorMapEncodeTiled failed with CUresult %d", what, (int)r); return B2_ERR_CUDA; }
+  return B2_OK;
+}
+
+int num_sms() {
+  static int n = 0;
+  if (n == 0) {
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0) {
+      cudaGetLastError();
+      n = B2_NUM_SMS;
+    }
+  }
+  return n;
+}
+
+template <int MODE, int A_MN, int B_MN>
+int launch(const CUtensorMap& ta, const CUtensorMap& tb, const Params& p, cudaStream_t stream) {
+  auto kern = umma_kernel<MODE, A_MN, B_MN>;
+  B2_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
+  const int units = p.num_m_blocks * p.n_splits;
+  const int grid = units < num_sms() ? units : num_sms();
+  kern<<<grid, 256, SMEM_BYTES, stream>>>(ta, tb, p);
+  B2_CHECK_CUDA(cudaGetLastError());
+  return B2_OK;
+}
+
+// operand [rows = M or N extent, K] -> tensor map; K-major: memory is [extent, ld] with K contiguous;
+// MN-major: memory is [K, ld] with the M/N extent contiguous.
+int make_operand_tmap(CUtensorMap* m, const void* ptr, int mn_major, long long extent, long long K, long long ld,
+                      int tile_extent, const char* what) {
+  if (!mn_major) return make_tmap(m, ptr, K, extent, ld, BK, tile_extent, what);
+  return make_tmap(m, ptr, extent, K, ld, 64, BK, what);
+}
+
+// Pick how many contiguous vocabulary ranges each 128-row block is split into so that the persistent
+// grid finishes with the least idle time (units are dealt round-robin to CTAs).
+int choose_splits(int num_m_blocks, int num_n_blocks, int grid) {
+  int best_s = 1; double best = 1e30;
+  const int smax = num_n_blocks < MAX_SPLITS ? num_n_blocks : MAX_SPLITS;
+  for (int S = 1; S <= smax; ++S) {
+    const long long units = (long long)num_m_blocks * S;
+    // CTA b handles units b, b+grid, ...; unit u has split s = u / num_m_blocks
+    double worst = 0;
+    const int ctas = units < grid ? (int)units : grid;
+    for (int b = 0; b < ctas; ++b) {
+      double t = 0;
+      for (long long u = b; u < units; u += grid) {
+        const int s = (int)(u / num_m_blocks);
+        const int tiles = (int)((long long)(s + 1) * num_n_blocks / S - (long long)s * num_n_blocks / S);
+        t += tiles + 0.15;   // per-unit start-up cost, in tile units
+      }
+      if (t > worst) worst = t;
+    }
+    if (worst < best - 1e-9) { best = worst; best_s = S; }
+  }
+  return best_s;
+}
+
+}  // namespace
+
+extern "C" int b2_gemm_bf16(const void* A, int a_mn_major, long long lda, const void* B, int b_mn_major, long long ldb,
+                            void* C, int c_dtype, long long ldc, int M, int N, int K, int accumulate, cudaStream_t stream) {
+  B2_REQUIRE(M >= 1 && N >= 1 && K >= 1, "b2_gemm_bf16: bad shape M=%d N=%d K=%d", M, N, K);
+  B2_REQUIRE(A && B && C, "b2_gemm_bf16: null pointer");
+  B2_REQUIRE(c_dtype == B2_F32 || c_dtype == B2_BF16, "b2_gemm_bf16: c_dtype must be 0 (f32) or 1 (bf16)");
+  B2_REQUIRE(ldc >= N, "b2_gemm_bf16: ldc < N");
+  CUtensorMap ta, tb;
+  int rc;
+  if ((rc = make_operand_tmap(&ta, A, a_mn_major, M, K, lda, BM, "b2_gemm_bf16 A")) != B2_OK) return rc;
+  if ((rc = make_operand_tmap(&tb, B, b_mn_major, N, K, ldb, BN, "b2_gemm_bf16 B")) != B2_OK) return rc;
+  Params p{};
+  p.M = M; p.N = N; p.K = K;
+  p.num_m_blocks = (M + BM - 1) / BM; p.num_n_blocks = (N + BN - 1) / BN; p.num_k_blocks = (K + BK - 1) / BK;
+  p.n_splits = p.num_n_blocks;
+  p.C = C; p.ldc = ldc; p.c_dtype = c_dtype; p.accumulate = accumulate;
+  if (!a_mn_major && !b_mn_major) return launch<MODE_GEMM, 0, 0>(ta, tb, p, stream);
+  if (!a_mn_major && b_mn_major) return launch<MODE_GEMM, 0, 1>(ta, tb, p, stream);
+  if (a_mn_major && !b_mn_major) return launch<MODE_GEMM, 1, 0>(ta, tb, p, stream);
+  return launch<MODE_GEMM, 1, 1>(ta, tb, p, stream);
+}
+
+extern "C" size_t b2_lmhead_ce_workspace_bytes(long long N) {
+  const long long npad = (N + BM - 1) / BM * BM;
+  return (size_t)MAX_SPLITS * (size_t)npad * sizeof(float2);
+}
+
+extern "C" int b2_lmhead_ce_fwd(const void* H, long long ldh, const void* W, long long ldw, const float* bias,
+                                const long long* labels, long long N, int D, int V, int shift_T, long long ignore_index,
+                                int round_logits_bf16, void* workspace, size_t workspace_bytes, float* lse, float* zt,
+                                float* loss_out, long long* n_valid_out, int* err_out, cudaStream_t stream) {
+  B2_REQUIRE(N >= 0 && D >= 1 && V >= 1, "b2_lmhead_ce_fwd: bad shape N=%lld D=%d V=%d", N, D, V);
+  B2_REQUIRE(N < (1ll << 31) - BM, "b2_lmhead_ce_fwd: N too large");
+  B2_REQUIRE(loss_out && n_valid_out, "b2_lmhead_ce_fwd: null output");
+  B2_REQUIRE(shift_T == 0 || (shift_T > 0 && N % shift_T == 0), "b2_lmhead_ce_fwd: N must be a multiple of shift_T");
+  if (N > 0) {
+    B2_REQUIRE(H && W && labels && lse && zt && workspace, "b2_lmhead_ce_fwd: null buffer");
+    B2_REQUIRE(workspace_bytes >= b2_lmhead_ce_workspace_bytes(N), "b2_lmhead_ce_fwd: workspace too small (%zu < %zu)",
+               workspace_bytes, b2_lmhead_ce_workspace_bytes(N));
+    B2_REQUIRE(b2_aligned(workspace, 16), "b2_lmhead_ce_fwd: workspace must be 16-byte aligned");
+    CUtensorMap ta, tb;
+    int rc;
+    if ((rc = make_operand_tmap(&ta, H, 0, N, D, ldh, BM, "b2_lmhead_ce_fwd H")) != B2_OK) return rc;
+    if ((rc = make_operand_tmap(&tb, W, 0, V, D, ldw, BN, "b2_lmhead_ce_fwd W")) != B2_OK) return rc;
+    Params p{};
+    p.M = (int)N; p.N = V; p.K = D;
+    p.num_m_blocks = (int)((N + BM - 1) / BM); p.num_n_blocks = (V + BN - 1) / BN; p.num_k_blocks = (D + BK - 1) / BK;
+    p.n_splits = choose_splits(p.num_m_blocks, p.num_n_blocks, num_sms());
+    p.labels = labels; p.shift_T = shift_T; p.ignore_index = ignore_index; p.row0 = 0;
+    p.bias = bias; p.round_bf16 = round_logits_bf16;
+    p.part = static_cast<float2*>(workspace); p.part_stride = (long long)p.num_m_blocks * BM; p.zt = zt;
+    if ((rc = launch<MODE_CE_FWD, 0, 0>(ta, tb, p, stream)) != B2_OK) return rc;
+    ce_combine_kernel<<<(unsigned)((N + 255) / 256), 256, 0, stream>>>(p.part, p.part_stride, p.n_splits, N, lse);
+    B2_CHECK_CUDA(cudaGetLastError());
+  }
+  return b2_ce_finalize_launch(lse, zt, labels, N, V, shift_T, ignore_index, loss_out, n_valid_out, err_out, stream);
+}
+
+extern "C" int b2_lmhead_ce_bwd_dlogits(const void* H, long long ldh, const void* W, long long ldw, const float* bias,
+                                        const long long* labels, long long row0, long long rows, int D, int V, int shift_T,
+                                        long long ignore_index, int round_logits_bf16, const float* lse,
+                                        const float* gscale_dev, void* dlogits, long long ldd, cudaStream_t stream) {
+  if (rows == 0) return B2_OK;
+  B2_REQUIRE(rows > 0 && row0 >= 0 && D >= 1 && V >= 1, "b2_lmhead_ce_bwd_dlogits: bad shape rows=%lld D=%d V=%d", rows, D, V);
+  B2_REQUIRE(rows < (1ll << 31) - BM, "b2_lmhead_ce_bwd_dlogits: too many rows");
+  B2_REQUIRE(H && W && labels && lse && gscale_dev && dlogits, "b2_lmhead_ce_bwd_dlogits: null buffer");
+  B2_REQUIRE(ldd >= V && ldd % 8 == 0, "b2_lmhead_ce_bwd_dlogits: ldd must be >= V and a multiple of 8");
+  B2_REQUIRE(b2_aligned(dlogits, 16), "b2_lmhead_ce_bwd_dlogits: dlogits must be 16-byte aligned");
+  CUtensorMap ta, tb;
+  int rc;
+  if ((rc = make_operand_tmap(&ta, H, 0, rows, D, ldh, BM, "b2_lmhead_ce_bwd_dlogits H")) != B2_OK) return rc;
+  if ((rc = make_operand_tmap(&tb, W, 0, V, D, ldw, BN, "b2_lmhead_ce_bwd_dlogits W")) != B2_OK) return rc;
+  Params p{};
+  p.M = (int)rows; p.N = V; p.K = D;
+  p.num_m_blocks = (int)((rows + BM - 1) / BM); p.num_n_blocks = (V + BN - 1) / BN; p.num_k_blocks = (D + BK - 1) / BK;
+  p.n_splits = p.num_n_blocks;
+  p.labels = labels; p.shift_T = shift_T; p.ignore_index = ignore_index; p.row0 = row0;
+  p.bias = bias; p.round_bf16 = round_logits_bf16;
+  p.lse = lse; p.gscale = gscale_dev; p.dlogits = static_cast<__nv_bfloat16*>(dlogits); p.ldd = ldd;
+  return launch<MODE_CE_BWD, 0, 0>(ta, tb, p, stream);
+}

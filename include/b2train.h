@@ -1,0 +1,125 @@
+/* b2train.h — C ABI of libb2train.so: the B200 (sm_100a) kernels for the data-parallel training-step
+ * tail of ericehanley/gke-ray-train (LM head + cross-entropy, gradient norm/clip, AdamW, peer-memory
+ * gradient all-reduce).
+ *
+ * Conventions (all entry points):
+ *   - plain pointers and sizes only; every pointer is a CUDA device pointer unless stated otherwise;
+ *   - the caller owns every buffer; nothing is allocated or freed on the caller's behalf unless the
+ *     function's name says alloc/open/free/close;
+ *   - work is enqueued asynchronously on `stream` (a cudaStream_t passed as void*); the call returns
+ *     before the kernels run;
+ *   - return value: 0 = ok, <0 = error (B2_ERR_*); b2_last_error() gives the message for the calling
+ *     thread. Nothing throws;
+ *   - dtype codes: B2_F32 = 0, B2_BF16 = 1. Buffers must be 16-byte aligned.
+ *
+ * "ref:" citations name the file:line of the reference (ericehanley/gke-ray-train) call that the entry
+ * point replaces; "$SP" is the site-packages tree of the third-party library that call lands in.
+ */
+#ifndef B2TRAIN_H
+#define B2TRAIN_H
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define B2_OK 0
+#define B2_ERR_INVALID (-1)
+#define B2_ERR_CUDA (-2)
+#define B2_ERR_LIMIT (-3)
+#define B2_ERR_STATE (-4)
+#define B2_F32 0
+#define B2_BF16 1
+
+typedef void* b2_stream_t; /* cudaStream_t */
+
+/* ---- library ------------------------------------------------------------------------------------ */
+int b2_version(void);                 /* 100 = 0.1.0 */
+const char* b2_last_error(void);      /* message of the last failing call on this thread */
+int b2_device_count(void);            /* CUDA devices visible to this process (0 if none / no driver) */
+
+/* ---- F3: fused AdamW --------------------------------------------------------------------------------
+ * Replaces optimizer.step() of torch.optim.AdamW — ref: ray-jobs/pytorch_llm_ray.py:236,278 (lr 3e-4,
+ * weight_decay 0.01) and the HF Trainer optimizer configured by ref: ray-jobs/fine_tune_config.json:15-17.
+ * Arithmetic: $SP/torch/optim/adam.py:347-552 (decoupled weight decay, amsgrad off, maximize off).
+ * One pass over n elements of p (params), g (grads), m (exp_avg), v (exp_avg_sq); `step` is the 1-based
+ * step count AFTER the increment torch performs; bias corrections are formed in double on the host.
+ * gscale_dev (nullable): device float; g is multiplied by it (and rounded to g's dtype) before use —
+ * this is where clip_grad_norm_'s coefficient is applied without a separate pass over the gradients. */
+int b2_adamw(void* p, const void* g, void* m, void* v, size_t n, int p_dtype, int g_dtype, int state_dtype,
+             double lr, double beta1, double beta2, double eps, double weight_decay, long long step,
+             const float* gscale_dev, b2_stream_t stream);
+
+/* ---- gradient norm and clipping ------------------------------------------------------------------
+ * Replace torch.nn.utils.clip_grad_norm_ — ref: ray-jobs/pytorch_llm_ray.py:277 (max_norm 1.0); HF
+ * MAX_GRAD_NORM ref: ray-jobs/fine_tune_config.json:19. Arithmetic: $SP/torch/nn/utils/clip_grad.py:50-183.
+ * b2_sumsq: out[0] (=, or += when accumulate!=0) sum of squares of g[0..n). `scratch` must hold
+ *   b2_sumsq_scratch_bytes() bytes, be zero-filled once before its first use, and not be shared by calls
+ *   that may overlap on the GPU.
+ * b2_clip_coef: total = sqrt(sum of parts[0..nparts)); norm_out[0] = total;
+ *   coef_out[0] = min(1, max_norm / (total + 1e-6)). Either output may be NULL.
+ * b2_scale: g[0..n) *= coef_dev[0] in place. */
+size_t b2_sumsq_scratch_bytes(void);
+int b2_sumsq(const void* g, size_t n, int dtype, float* scratch, float* out, int accumulate, b2_stream_t stream);
+int b2_clip_coef(const float* sumsq_parts, int nparts, float max_norm, float* norm_out, float* coef_out,
+                 b2_stream_t stream);
+int b2_scale(void* g, size_t n, int dtype, const float* coef_dev, b2_stream_t stream);
+
+/* ---- cross-entropy over materialised logits -------------------------------------------------------
+ * Replace nn.CrossEntropyLoss()(outputs.reshape(-1,V), targets.reshape(-1)) — ref:
+ * ray-jobs/pytorch_llm_ray.py:237,275 (labels pre-shifted by TextDataset, ref :116-119).
+ * logits: [N, ld] row-major, first V columns used. labels: int64 [N].
+ * shift_T: 0 = labels already aligned with rows; T>0 = rows are [B, T] and row (b,t) is scored against
+ *   labels[b, t+1], the last position of each sequence being ignored (HF ForCausalLMLoss,
+ *   $SP/transformers/loss/loss_utils.py:45-67).
+ * Outputs: lse[N] (log-sum-exp per row), zt[N] (label logit per row), loss_out[0] = sum over non-ignored
+ *   rows of (lse - z), loss_out[1] = that sum / n_valid (NaN when n_valid == 0, as torch's mean);
+ *   n_valid_out[0] = number of rows whose label != ignore_index (int64, exact);
+ *   err_out[0] (nullable) = 1 if any non-ignored label is outside [0, V) — torch raises there; here the
+ *   loss is additionally set to NaN.
+ * b2_ce_rows_bwd: dlogits[i, j] = (exp(logits[i,j] - lse[i]) - [j == label_i]) * gscale_dev[0] for
+ *   non-ignored rows, 0 otherwise; dlogits may alias logits. gscale = grad_output / n_valid for 'mean'. */
+int b2_ce_rows_fwd(const void* logits, int dtype, long long N, long long V, long long ld, const long long* labels,
+                   int shift_T, long long ignore_index, float* lse, float* zt, float* loss_out,
+                   long long* n_valid_out, int* err_out, b2_stream_t stream);
+int b2_ce_rows_bwd(const void* logits, int dtype, long long N, long long V, long long ld, const long long* labels,
+                   int shift_T, long long ignore_index, const float* lse, const float* gscale_dev, void* dlogits,
+                   b2_stream_t stream);
+
+/* ---- F1: LM head fused with cross-entropy (tcgen05 / TMEM / TMA) ------------------------------------
+ * Replaces lm_head(hidden) followed by the causal-LM loss — ref: ray-jobs/fine_tune_llama_ray.py:333
+ * (trainer.train() -> $SP/transformers/models/llama/modeling_llama.py:486-491 ->
+ * $SP/transformers/loss/loss_utils.py:45-67) and BasicLLM.fc_out + criterion, ref:
+ * ray-jobs/pytorch_llm_ray.py:87,104,237,275. The [N, V] logits are never written to memory.
+ * H: [N, ldh] bf16 hidden states (D used columns); W: [V, ldw] bf16 (nn.Linear weight layout);
+ * bias: fp32 [V] or NULL. ldh, ldw multiples of 8.
+ * round_logits_bf16 != 0 rounds each logit to bf16 before the soft-max, which is what the reference's
+ *   bf16 lm_head followed by .float() computes.
+ * workspace: b2_lmhead_ce_workspace_bytes(N) bytes of scratch, contents irrelevant.
+ * Outputs as for b2_ce_rows_fwd. */
+size_t b2_lmhead_ce_workspace_bytes(long long N);
+int b2_lmhead_ce_fwd(const void* H, long long ldh, const void* W, long long ldw, const float* bias,
+                     const long long* labels, long long N, int D, int V, int shift_T, long long ignore_index,
+                     int round_logits_bf16, void* workspace, size_t workspace_bytes, float* lse, float* zt,
+                     float* loss_out, long long* n_valid_out, int* err_out, b2_stream_t stream);
+/* Backward, step 1: recomputes the logits of rows [row0, row0+rows) and writes
+ *   dlogits[r, j] = (exp(logit - lse[row0+r]) - [j == label]) * gscale_dev[0]   (bf16, [rows, ldd], ldd % 8 == 0)
+ * H points at row row0 of the hidden states; labels and lse are the full arrays (indexed by row0 + r).
+ * dH and dW then follow from two b2_gemm_bf16 calls on this chunk. */
+int b2_lmhead_ce_bwd_dlogits(const void* H, long long ldh, const void* W, long long ldw, const float* bias,
+                             const long long* labels, long long row0, long long rows, int D, int V, int shift_T,
+                             long long ignore_index, int round_logits_bf16, const float* lse,
+                             const float* gscale_dev, void* dlogits, long long ldd, b2_stream_t stream);
+/* Plain bf16 GEMM on the same tcgen05 mainloop: C[M,N] (+)= A[M,K] * B[N,K]^T, fp32 accumulate.
+ * a_mn_major = 0: A stored [M, lda] with K contiguous; 1: A stored [K, lda] with M contiguous. Same for B
+ * with N. C row-major [M, ldc], fp32 or bf16; accumulate != 0 adds to the existing C.
+ * Used for dH = dlogits * W and dW += dlogits^T * H, replacing the autograd GEMMs of nn.Linear
+ * (ref: the loss.backward() at ray-jobs/pytorch_llm_ray.py:276). */
+int b2_gemm_bf16(const void* A, int a_mn_major, long long lda, const void* B, int b_mn_major, long long ldb, void* C,
+                 int c_dtype, long long ldc, int M, int N, int K, int accumulate, b2_stream_t stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B2TRAIN_H */
