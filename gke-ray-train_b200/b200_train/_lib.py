@@ -17,6 +17,12 @@ class B2Error(RuntimeError):
     pass
 
 
+class AdamWGroup(ctypes.Structure):
+    """Mirror of B2AdamWGroup in include/b2train.h."""
+    _fields_ = [("lr", c_double), ("beta1", c_double), ("beta2", c_double), ("eps", c_double),
+                ("weight_decay", c_double), ("step", c_longlong)]
+
+
 if not os.path.exists(LIB_PATH):
     raise ImportError(
         f"{LIB_PATH} not found: build it with `python gke-ray-train_b200/build.py` "
@@ -30,6 +36,8 @@ _SIGS = {
     "b2_device_count": (c_int, []),
     "b2_adamw": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_size_t, c_int, c_int, c_int, c_double, c_double,
                          c_double, c_double, c_double, c_longlong, c_void_p, c_void_p]),
+    "b2_adamw_grouped": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_size_t, c_int, c_int, c_int, c_void_p,
+                                 c_void_p, c_int, c_void_p, c_void_p]),
     "b2_sumsq_scratch_bytes": (c_size_t, []),
     "b2_sumsq": (c_int, [c_void_p, c_size_t, c_int, c_void_p, c_void_p, c_int, c_void_p]),
     "b2_clip_coef": (c_int, [c_void_p, c_int, c_float, c_void_p, c_void_p, c_void_p]),
@@ -47,6 +55,15 @@ _SIGS = {
                                          c_void_p, c_longlong, c_void_p]),
     "b2_gemm_bf16": (c_int, [c_void_p, c_int, c_longlong, c_void_p, c_int, c_longlong, c_void_p, c_int, c_longlong,
                              c_int, c_int, c_int, c_int, c_void_p]),
+    "b2_peer_flags_bytes": (c_size_t, []),
+    "b2_symm_alloc": (c_int, [c_size_t, c_void_p, c_void_p]),
+    "b2_symm_open": (c_int, [c_void_p, c_void_p]),
+    "b2_symm_close": (c_int, [c_void_p]),
+    "b2_symm_free": (c_int, [c_void_p]),
+    "b2_peer_allreduce": (c_int, [c_void_p, c_void_p, c_int, c_int, c_size_t, c_size_t, c_int, c_float, ctypes.c_uint,
+                                  c_int, c_int, c_void_p]),
+    "b2_peer_allgather": (c_int, [c_void_p, c_void_p, c_int, c_int, c_size_t, c_size_t, c_int, ctypes.c_uint, c_void_p]),
+    "b2_peer_slice": (c_int, [c_size_t, c_int, c_int, c_int, c_void_p, c_void_p]),
 }
 
 for _name, (_res, _args) in _SIGS.items():
@@ -58,8 +75,9 @@ EXPORTS = tuple(_SIGS)
 
 # number of kernels this process has enqueued through the library (bench.py reports it)
 launch_count = 0
-_LAUNCHES = {"b2_adamw": 1, "b2_sumsq": 1, "b2_clip_coef": 1, "b2_scale": 1, "b2_ce_rows_fwd": 2,
-             "b2_ce_rows_bwd": 1, "b2_lmhead_ce_fwd": 3, "b2_lmhead_ce_bwd_dlogits": 1, "b2_gemm_bf16": 1}
+_LAUNCHES = {"b2_adamw": 1, "b2_adamw_grouped": 1, "b2_sumsq": 1, "b2_clip_coef": 1, "b2_scale": 1, "b2_ce_rows_fwd": 2,
+             "b2_ce_rows_bwd": 1, "b2_lmhead_ce_fwd": 3, "b2_lmhead_ce_bwd_dlogits": 1, "b2_gemm_bf16": 1,
+             "b2_peer_allreduce": 1, "b2_peer_allgather": 1}
 
 
 def call(name, *args):

@@ -87,9 +87,6 @@ def flatten_params(params, alloc=None):
             if f[0] not in existing:
                 existing.append(f[0])
             continue
-        if not p.is_cuda:
-            raise RuntimeError("b200_train: parameters must be on a CUDA device before they are flattened "
-                               "(there is no CPU path)")
         key = (p.device, p.dtype)
         if key not in groups:
             groups[key] = []

@@ -1,0 +1,197 @@
+"""Loss side of the step tail.
+
+* `CrossEntropyLoss` — drop-in for `nn.CrossEntropyLoss()` as used at ref: ray-jobs/pytorch_llm_ray.py:237,275
+  (materialised fp32 logits `[N, V]`, class-index targets, mean reduction, ignore_index -100).
+* `fused_lm_head_ce` / `FusedLMHeadCE` / `patch_causal_lm` — the LM head and the causal-LM loss in one tcgen05
+  kernel for bf16 models, replacing `lm_head(hidden)` + `ForCausalLMLoss` that `trainer.train()` reaches
+  (ref: ray-jobs/fine_tune_llama_ray.py:333 -> $SP/transformers/models/llama/modeling_llama.py:486-491 ->
+  $SP/transformers/loss/loss_utils.py:45-67).
+"""
+import torch
+import torch.nn as nn
+
+from . import ops
+from ._lib import B2Error
+
+DEFAULT_CHUNK_ROWS = 4096
+
+
+def _gscale(grad_out, result, reduction, num_items):
+    """Device scalar multiplying (softmax - onehot): grad_output / denominator. No host sync."""
+    g = grad_out.detach().to(torch.float32).reshape(1)
+    if num_items is not None:
+        if isinstance(num_items, torch.Tensor):
+            return g / num_items.to(g.device, torch.float32).reshape(1)
+        return g / float(num_items)
+    if reduction == "sum":
+        return g.clone()
+    return g / result.n_valid.to(torch.float32)
+
+
+def _pick_loss(result, reduction, num_items):
+    if num_items is not None:
+        if isinstance(num_items, torch.Tensor):
+            return result.loss[0] / num_items.to(result.loss.device, torch.float32)
+        return result.loss[0] / float(num_items)
+    return result.loss[0] if reduction == "sum" else result.loss[1]
+
+
+class _CERowsFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, logits, labels, ignore_index, reduction, check):
+        x = logits if logits.stride(-1) == 1 else logits.contiguous()
+        r = ops.ce_rows_fwd(x, labels, 0, ignore_index)
+        if check and int(r.err.item()):
+            raise IndexError("Target out of bounds for cross_entropy (label outside [0, V) and != ignore_index)")
+        ctx.save_for_backward(x, labels, r.lse, r.n_valid)
+        ctx.ignore_index, ctx.reduction = ignore_index, reduction
+        ctx.result = r
+        return _pick_loss(r, reduction, None).clone()
+
+    @staticmethod
+    def backward(ctx, grad_out):
+        x, labels, lse, n_valid = ctx.saved_tensors
+        gs = _gscale(grad_out, ctx.result, ctx.reduction, None)
+        d = ops.ce_rows_bwd(x, labels, lse, gs, 0, ctx.ignore_index)
+        return d, None, None, None, None
+
+
+class CrossEntropyLoss(nn.Module):
+    """`criterion = CrossEntropyLoss(); loss = criterion(outputs.reshape(-1, V), targets.reshape(-1))`.
+
+    check_labels=True makes an out-of-range target raise IndexError like torch (this costs one host sync per
+    call); with False the loss comes back NaN and `last_result.err` is set instead."""
+
+    def __init__(self, weight=None, size_average=None, ignore_index=-100, reduce=None, reduction="mean",
+                 label_smoothing=0.0, check_labels=False):
+        super().__init__()
+        if weight is not None or label_smoothing != 0.0 or size_average is not None or reduce is not None:
+            raise B2Error("b200_train.CrossEntropyLoss implements what the reference uses: no class weights, "
+                          "no label smoothing, reduction 'mean' or 'sum'")
+        if reduction not in ("mean", "sum"):
+            raise B2Error("reduction must be 'mean' or 'sum'")
+        self.ignore_index, self.reduction, self.check_labels = ignore_index, reduction, check_labels
+
+    def forward(self, input, target):
+        if input.dim() != 2 or target.dim() != 1:
+            raise B2Error("expected logits [N, V] and targets [N] (the reference reshapes to exactly this)")
+        return _CERowsFn.apply(input, target.contiguous(), self.ignore_index, self.reduction, self.check_labels)
+
+
+class _LMHeadCEFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, hidden, weight, bias, labels, shift_T, ignore_index, reduction, num_items, round_bf16, chunk_rows):
+        H = hidden if hidden.stride(-1) == 1 else hidden.contiguous()
+        bias32 = None if bias is None else bias.detach().to(torch.float32).contiguous()
+        r = ops.lmhead_ce_fwd(H, weight, labels, bias=bias32, shift_T=shift_T, ignore_index=ignore_index,
+                              round_logits_bf16=round_bf16)
+        ctx.save_for_backward(H, weight, labels, r.lse, r.n_valid)
+        ctx.bias32, ctx.has_bias = bias32, bias is not None
+        ctx.bias_dtype = None if bias is None else bias.dtype
+        ctx.cfg = (shift_T, ignore_index, reduction, num_items, round_bf16, chunk_rows)
+        ctx.result = r
+        return _pick_loss(r, reduction, num_items).clone()
+
+    @staticmethod
+    def backward(ctx, grad_out):
+        H, W, labels, lse, n_valid = ctx.saved_tensors
+        shift_T, ignore_index, reduction, num_items, round_bf16, chunk_rows = ctx.cfg
+        N, D = H.shape
+        V = W.shape[0]
+        gs = _gscale(grad_out, ctx.result, reduction, num_items)
+        ldd = (V + 7) // 8 * 8
+        chunk = min(N, chunk_rows)
+        dl = torch.empty(chunk, ldd, dtype=torch.bfloat16, device=H.device)
+        need_dH, need_dW = ctx.needs_input_grad[0], ctx.needs_input_grad[1]
+        dH = torch.empty(N, D, dtype=torch.bfloat16, device=H.device) if need_dH else None
+        n_chunks = (N + chunk - 1) // chunk
+        dW = None
+        if need_dW:
+            # one chunk: write bf16 directly; several: accumulate in fp32 and round once at the end, like the
+            # single fp32-accumulated GEMM of the reference's autograd
+            dW = torch.empty(V, D, dtype=torch.bfloat16 if n_chunks == 1 else torch.float32, device=H.device)
+        db = torch.zeros(V, dtype=torch.float32, device=H.device) if ctx.has_bias else None
+        for c in range(n_chunks):
+            r0 = c * chunk
+            rows = min(chunk, N - r0)
+            ops.lmhead_ce_bwd_dlogits(H, W, labels, lse, gs, r0, rows, dl, bias=ctx.bias32, shift_T=shift_T,
+                                      ignore_index=ignore_index, round_logits_bf16=round_bf16)
+            if need_dH:     # dH[rows, D] = dL[rows, V] @ W[V, D]      (B = W read MN-major)
+                ops.gemm_bf16(dl, W, dH[r0:r0 + rows], rows, D, V, a_mn_major=False, b_mn_major=True)
+            if need_dW:     # dW[V, D] += dL^T[V, rows] @ H[rows, D]   (A = dL and B = H both read MN-major)
+                ops.gemm_bf16(dl, H[r0:r0 + rows], dW, V, D, rows, a_mn_major=True, b_mn_major=True, accumulate=c > 0)
+            if db is not None:
+                db += dl[:rows, :V].sum(dim=0, dtype=torch.float32)
+        if dW is not None and dW.dtype != W.dtype:
+            dW = dW.to(W.dtype)
+        if db is not None:
+            db = db.to(ctx.bias_dtype)
+        return dH, dW, db, None, None, None, None, None, None, None
+
+
+def fused_lm_head_ce(hidden, weight, labels, bias=None, *, shift=True, ignore_index=-100, reduction="mean",
+                     num_items_in_batch=None, round_logits_bf16=True, chunk_rows=DEFAULT_CHUNK_ROWS):
+    """loss = CE(hidden @ weight.T (+bias), labels) without materialising the logits.
+
+    hidden [..., T, D] bf16, weight [V, D] bf16, labels [..., T] int64. shift=True applies the causal shift inside
+    (row t is scored against labels[t+1], the last position ignored) exactly as HF's ForCausalLMLoss; shift=False
+    expects pre-shifted labels (the reference's TextDataset, ref: ray-jobs/pytorch_llm_ray.py:116-119).
+    num_items_in_batch: HF gradient-accumulation normaliser — the loss is sum / num_items_in_batch."""
+    if hidden.dtype != torch.bfloat16 or weight.dtype != torch.bfloat16:
+        raise B2Error("fused_lm_head_ce takes bfloat16 hidden states and weight (use CrossEntropyLoss for fp32 logits)")
+    T = hidden.shape[-2] if hidden.dim() >= 2 else 1
+    H2 = hidden.reshape(-1, hidden.shape[-1])
+    y = labels.reshape(-1).contiguous()
+    if y.device != H2.device:
+        y = y.to(H2.device)
+    return _LMHeadCEFn.apply(H2, weight, bias, y, T if shift else 0, ignore_index, reduction, num_items_in_batch,
+                             round_logits_bf16, chunk_rows)
+
+
+class FusedLMHeadCE(nn.Module):
+    """Module form: owns nothing, borrows the LM head's weight (tied weights keep working)."""
+
+    def __init__(self, lm_head, shift=True, ignore_index=-100, reduction="mean", round_logits_bf16=True,
+                 chunk_rows=DEFAULT_CHUNK_ROWS):
+        super().__init__()
+        self.lm_head = lm_head
+        self.shift, self.ignore_index, self.reduction = shift, ignore_index, reduction
+        self.round_logits_bf16, self.chunk_rows = round_logits_bf16, chunk_rows
+
+    def forward(self, hidden, labels, num_items_in_batch=None):
+        return fused_lm_head_ce(hidden, self.lm_head.weight, labels, getattr(self.lm_head, "bias", None),
+                                shift=self.shift, ignore_index=self.ignore_index, reduction=self.reduction,
+                                num_items_in_batch=num_items_in_batch, round_logits_bf16=self.round_logits_bf16,
+                                chunk_rows=self.chunk_rows)
+
+
+def patch_causal_lm(model, chunk_rows=DEFAULT_CHUNK_ROWS):
+    """Re-routes `model(input_ids, labels=...)` of a HF *ForCausalLM / GPT2LMHeadModel through the fused kernel:
+    the backbone runs as before, the logits are never formed, and the returned output carries `loss` (logits=None).
+    Calls without labels are untouched. Returns the same model object."""
+    from transformers.modeling_outputs import CausalLMOutputWithPast
+
+    head = model.get_output_embeddings()
+    backbone = model.base_model
+    if head is None or backbone is model:
+        raise B2Error("patch_causal_lm: model has no separate backbone / output embedding")
+    fused = FusedLMHeadCE(head, shift=True, chunk_rows=chunk_rows)
+    orig_forward = model.forward
+
+    def forward(input_ids=None, labels=None, num_items_in_batch=None, **kw):
+        if labels is None or head.weight.dtype != torch.bfloat16:
+            if num_items_in_batch is not None:
+                kw["num_items_in_batch"] = num_items_in_batch
+            return orig_forward(input_ids=input_ids, labels=labels, **kw)
+        kw.pop("return_dict", None)
+        kw.pop("logits_to_keep", None)
+        out = backbone(input_ids=input_ids, **kw)
+        hidden = out[0]
+        loss = fused(hidden, labels, num_items_in_batch=num_items_in_batch)
+        return CausalLMOutputWithPast(loss=loss, logits=None, past_key_values=getattr(out, "past_key_values", None),
+                                      hidden_states=getattr(out, "hidden_states", None),
+                                      attentions=getattr(out, "attentions", None))
+
+    model.forward = forward
+    model._b2_fused_head = fused
+    return model

@@ -41,6 +41,23 @@ def adamw_(p, g, m, v, *, lr, beta1=0.9, beta2=0.999, eps=1e-8, weight_decay=1e-
              ptr(gscale), stream_ptr())
 
 
+def adamw_grouped_(p, g, m, v, chunk_group, groups, gscale=None):
+    """Fused AdamW over a flat buffer holding several param_groups. `chunk_group`: uint8 device tensor, one entry
+    per 64 elements; `groups`: list of dicts(lr, beta1, beta2, eps, weight_decay, step)."""
+    import ctypes
+    require_cuda(p, g, m, v, chunk_group, gscale)
+    n = p.numel()
+    if chunk_group.dtype != torch.uint8 or chunk_group.numel() * 64 != n:
+        raise B2Error("adamw_grouped_: chunk_group must be uint8 with one entry per 64 elements")
+    arr = (_lib.AdamWGroup * len(groups))()
+    for i, h in enumerate(groups):
+        arr[i] = _lib.AdamWGroup(float(h["lr"]), float(h["beta1"]), float(h["beta2"]), float(h["eps"]),
+                                 float(h["weight_decay"]), int(h["step"]))
+    with torch.cuda.device(p.device):
+        call("b2_adamw_grouped", ptr(p), ptr(g), ptr(m), ptr(v), n, dtype_code(p.dtype), dtype_code(g.dtype),
+             dtype_code(m.dtype), ptr(chunk_group), ctypes.addressof(arr), len(groups), ptr(gscale), stream_ptr())
+
+
 def sumsq(g, out=None, accumulate=False):
     """Sum of squares of a flat tensor -> 1-element fp32 device tensor (no host sync)."""
     require_cuda(g)

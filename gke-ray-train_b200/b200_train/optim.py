@@ -1,0 +1,150 @@
+"""b200_train.AdamW — drop-in for torch.optim.AdamW on the reference's step tail.
+
+ref: ray-jobs/pytorch_llm_ray.py:236 `optim.AdamW(model.parameters(), lr=lr, weight_decay=0.01)`, :273
+`optimizer.zero_grad(set_to_none=True)`, :278 `optimizer.step()`, :302 `optimizer.state_dict()`; the HF Trainer
+AdamW with two param_groups configured by ref: ray-jobs/fine_tune_config.json:15-17.
+
+Same constructor, `param_groups` (so LambdaLR / HF schedulers mutate `group["lr"]` as usual), and a
+`state_dict()` in torch's layout (`step`, `exp_avg`, `exp_avg_sq` per parameter). The update itself is one
+`b2_adamw_grouped` launch per flat buffer instead of ~9 foreach launches per dtype group.
+"""
+import torch
+
+from . import ops
+from ._lib import B2Error
+from .flat import flatten_params
+
+
+class AdamW(torch.optim.Optimizer):
+    def __init__(self, params, lr=1e-3, betas=(0.9, 0.999), eps=1e-8, weight_decay=1e-2, amsgrad=False, *,
+                 maximize=False, foreach=None, capturable=False, differentiable=False, fused=None,
+                 state_dtype=None):
+        if isinstance(lr, torch.Tensor):
+            raise B2Error("b200_train.AdamW: lr must be a Python float (it is a per-launch scalar)")
+        if not 0.0 <= lr:
+            raise ValueError(f"Invalid learning rate: {lr}")
+        if not 0.0 <= eps:
+            raise ValueError(f"Invalid epsilon value: {eps}")
+        if not 0.0 <= betas[0] < 1.0:
+            raise ValueError(f"Invalid beta parameter at index 0: {betas[0]}")
+        if not 0.0 <= betas[1] < 1.0:
+            raise ValueError(f"Invalid beta parameter at index 1: {betas[1]}")
+        if not 0.0 <= weight_decay:
+            raise ValueError(f"Invalid weight_decay value: {weight_decay}")
+        if amsgrad or maximize or capturable or differentiable:
+            raise B2Error("b200_train.AdamW supports the configuration the reference uses: amsgrad=False, "
+                          "maximize=False, capturable=False, differentiable=False")
+        # `foreach` / `fused` only choose among torch's own implementations; accepted and ignored.
+        defaults = dict(lr=lr, betas=betas, eps=eps, weight_decay=weight_decay, amsgrad=False, maximize=False,
+                        foreach=None, capturable=False, differentiable=False, fused=None,
+                        decoupled_weight_decay=True)
+        super().__init__(params, defaults)
+        if len(self.param_groups) > 8:
+            raise B2Error("b200_train.AdamW: at most 8 param_groups")
+        self._state_dtype = state_dtype
+        self._buffers = None
+        self._chunk_group = {}
+        self._group_step = []      # one shared CPU step tensor per param_group (torch keeps one per parameter)
+
+    # ------------------------------------------------------------------ set-up (first step)
+    def _setup(self):
+        all_params = [p for g in self.param_groups for p in g["params"]]
+        for p in all_params:
+            if p.grad is not None and p.grad.is_sparse:
+                raise RuntimeError("AdamW does not support sparse gradients")
+        self._buffers = flatten_params(all_params)
+        gid = {}
+        for gi, g in enumerate(self.param_groups):
+            for p in g["params"]:
+                gid[id(p)] = gi
+        self._share_steps()
+        for buf in self._buffers:
+            sdt = self._state_dtype or buf.dtype      # torch: zeros_like(p) -> state dtype = param dtype
+            if buf.exp_avg is None:
+                buf.exp_avg = torch.zeros(buf.numel, dtype=sdt, device=buf.device)
+                buf.exp_avg_sq = torch.zeros(buf.numel, dtype=sdt, device=buf.device)
+            table = torch.full((buf.numel // 64,), 255, dtype=torch.uint8)
+            for p, o in zip(buf.params, buf.offsets):
+                if id(p) in gid:
+                    table[o // 64:(o + p.numel() + 63) // 64] = gid[id(p)]
+            self._chunk_group[id(buf)] = table.to(buf.device)
+            buf.optimizer_attached = True
+            for p, o in zip(buf.params, buf.offsets):
+                if id(p) not in gid:
+                    continue
+                st = self.state[p]
+                # views into the flat state: state_dict() keeps torch's per-parameter layout
+                st["exp_avg"] = buf.exp_avg[o:o + p.numel()].view(p.shape)
+                st["exp_avg_sq"] = buf.exp_avg_sq[o:o + p.numel()].view(p.shape)
+
+    def _share_steps(self):
+        """All parameters of a group advance together, so they share one `step` tensor (saved per parameter by
+        state_dict(), as torch does)."""
+        self._group_step = []
+        for g in self.param_groups:
+            cur = 0.0
+            for p in g["params"]:
+                st = self.state.get(p)
+                if st and "step" in st:
+                    cur = max(cur, float(st["step"]))
+            t = torch.tensor(cur, dtype=torch.float32)
+            self._group_step.append(t)
+            for p in g["params"]:
+                if p.requires_grad:
+                    self.state[p]["step"] = t
+
+    def flat_buffers(self):
+        if self._buffers is None:
+            self._setup()
+        return self._buffers
+
+    # ------------------------------------------------------------------ torch.optim.Optimizer surface
+    def zero_grad(self, set_to_none=True):
+        """ref :273 calls zero_grad(set_to_none=True). The gradients live in a persistent flat buffer that the
+        kernels (and the peer-memory all-reduce) address directly, so they are zero-filled in place rather than
+        dropped; a backward pass accumulates into zeros, which gives the same values as into None."""
+        if self._buffers is None:
+            return super().zero_grad(set_to_none=set_to_none)
+        for buf in self._buffers:
+            buf.zero_grad()
+            buf.install_grads()
+
+    @torch.no_grad()
+    def step(self, closure=None):
+        loss = None
+        if closure is not None:
+            with torch.enable_grad():
+                loss = closure()
+        first = self._buffers is None
+        if first:
+            self._setup()
+        for buf in self._buffers:
+            buf.install_grads()          # adopts grads autograd allocated before the buffers existed
+        hyper = []
+        for g, t in zip(self.param_groups, self._group_step):
+            t += 1
+            b1, b2 = g["betas"]
+            hyper.append(dict(lr=g["lr"], beta1=b1, beta2=b2, eps=g["eps"], weight_decay=g["weight_decay"],
+                              step=int(t.item())))
+        for buf in self._buffers:
+            ops.adamw_grouped_(buf.data, buf.grad, buf.exp_avg, buf.exp_avg_sq, self._chunk_group[id(buf)], hyper,
+                               gscale=buf.pending_coef)
+            buf.pending_coef = None
+        return loss
+
+    def load_state_dict(self, state_dict):
+        super().load_state_dict(state_dict)
+        if self._buffers is None:
+            return
+        # re-home the loaded tensors into the flat state so the kernels see them
+        for buf in self._buffers:
+            for p, o in zip(buf.params, buf.offsets):
+                st = self.state.get(p)
+                if not st:
+                    continue
+                for key, flat in (("exp_avg", buf.exp_avg), ("exp_avg_sq", buf.exp_avg_sq)):
+                    view = flat[o:o + p.numel()].view(p.shape)
+                    if st[key].data_ptr() != view.data_ptr():
+                        view.copy_(st[key])
+                        st[key] = view
+        self._share_steps()

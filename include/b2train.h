@@ -51,6 +51,15 @@ int b2_adamw(void* p, const void* g, void* m, void* v, size_t n, int p_dtype, in
              double lr, double beta1, double beta2, double eps, double weight_decay, long long step,
              const float* gscale_dev, b2_stream_t stream);
 
+/* Grouped variant for optimizers with several param_groups (HF Trainer builds two: weight decay on / off,
+ * $SP/transformers/trainer.py:1157-1170) laid out in ONE flat buffer: chunk_group_dev[c] (uint8, device) names the
+ * group (0..ngroups-1, at most 8) of elements [64c, 64c+64); 255 = leave the chunk untouched. n % 64 == 0.
+ * groups_host is a HOST array of ngroups hyper-parameter records. */
+typedef struct B2AdamWGroup { double lr, beta1, beta2, eps, weight_decay; long long step; } B2AdamWGroup;
+int b2_adamw_grouped(void* p, const void* g, void* m, void* v, size_t n, int p_dtype, int g_dtype, int state_dtype,
+                     const uint8_t* chunk_group_dev, const B2AdamWGroup* groups_host, int ngroups,
+                     const float* gscale_dev, b2_stream_t stream);
+
 /* ---- gradient norm and clipping ------------------------------------------------------------------
  * Replace torch.nn.utils.clip_grad_norm_ — ref: ray-jobs/pytorch_llm_ray.py:277 (max_norm 1.0); HF
  * MAX_GRAD_NORM ref: ray-jobs/fine_tune_config.json:19. Arithmetic: $SP/torch/nn/utils/clip_grad.py:50-183.
@@ -118,6 +127,41 @@ int b2_lmhead_ce_bwd_dlogits(const void* H, long long ldh, const void* W, long l
  * (ref: the loss.backward() at ray-jobs/pytorch_llm_ray.py:276). */
 int b2_gemm_bf16(const void* A, int a_mn_major, long long lda, const void* B, int b_mn_major, long long ldb, void* C,
                  int c_dtype, long long ldc, int M, int N, int K, int accumulate, b2_stream_t stream);
+
+/* ---- F2: gradient all-reduce over peer memory (NVLink 5 / NVSwitch) ----------------------------------
+ * Replaces the bucket all-reduce (+ the grad / world_size copy-in) that DistributedDataParallel performs during
+ * loss.backward() once ray.train.torch.prepare_model has wrapped the model — ref: ray-jobs/pytorch_llm_ray.py:230,276;
+ * $SP/torch/nn/parallel/distributed.py:1185-1280, $SP/torch/distributed/algorithms/ddp_comm_hooks/default_hooks.py:19-31.
+ *
+ * Symmetric memory: b2_symm_alloc cudaMallocs `bytes` (zero-filled) and returns a 64-byte CUDA IPC handle that the
+ * other processes of the job turn into a mapping of that memory with b2_symm_open (exchange the handles over the
+ * process group the launcher already set up). The owner frees with b2_symm_free after every peer has
+ * b2_symm_close'd its mapping.
+ * Flag block: each rank owns b2_peer_flags_bytes() bytes of symmetric memory, zero-filled once, used for the
+ * in-kernel barriers and the sum-of-squares exchange.
+ *
+ * peer_bufs / peer_flags: HOST arrays of `world` device pointers — entry k addresses rank k's buffer / flag block
+ * as mapped in THIS process (entry `rank` is the local allocation). world <= 8.
+ * b2_peer_allreduce, in place on elements [offset_elems, offset_elems + n) of every rank's buffer:
+ *   buf[i] <- round_dtype(scale * sum_k buf_k[i]) on all ranks (scale = 1/world for DDP's mean), bit-identical
+ *   everywhere. want_sumsq != 0 additionally leaves, in each rank's flag block, float slot 32 + k = sum of squares
+ *   of the reduced values of rank k's slice (k = 0..world-1) — feed those `world` floats to b2_clip_coef.
+ *   scatter_only != 0 stores the reduced slice of rank r on rank r only (reduce-scatter; see b2_peer_slice).
+ * b2_peer_allgather: pushes this rank's slice of the buffer to every peer (used for updated parameters).
+ * `epoch` must increase by one on every collective call, identically on all ranks (start at 1).
+ * Every rank must enqueue the same sequence of calls; the kernels wait for one another inside the GPU, so each
+ * rank needs its own device. A peer that never arrives makes the kernel trap after ~20 s instead of hanging. */
+size_t b2_peer_flags_bytes(void);
+int b2_symm_alloc(size_t bytes, void** dptr, unsigned char handle[64]);
+int b2_symm_open(const unsigned char handle[64], void** dptr);
+int b2_symm_close(void* dptr);
+int b2_symm_free(void* dptr);
+int b2_peer_allreduce(void* const* peer_bufs, uint32_t* const* peer_flags, int world, int rank, size_t offset_elems,
+                      size_t n, int dtype, float scale, unsigned epoch, int want_sumsq, int scatter_only,
+                      b2_stream_t stream);
+int b2_peer_allgather(void* const* peer_bufs, uint32_t* const* peer_flags, int world, int rank, size_t offset_elems,
+                      size_t n, int dtype, unsigned epoch, b2_stream_t stream);
+int b2_peer_slice(size_t n, int dtype, int world, int rank, size_t* begin, size_t* end);
 
 #ifdef __cplusplus
 }

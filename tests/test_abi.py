@@ -1,0 +1,89 @@
+"""The C-ABI shared library loads without a GPU, exports every symbol include/b2train.h declares, and rejects bad
+arguments with an error code + message instead of launching anything."""
+import ctypes
+import os
+import re
+
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+HEADER = os.path.join(ROOT, "include", "b2train.h")
+
+
+@pytest.fixture(scope="module")
+def lib():
+    from b200_train import _lib
+    return _lib
+
+
+def declared_symbols():
+    text = open(HEADER).read()
+    text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
+    return sorted(set(re.findall(r"\b(b2_[a-z0-9_]+)\s*\(", text)))
+
+
+def test_header_declares_something():
+    names = declared_symbols()
+    assert "b2_adamw" in names and "b2_lmhead_ce_fwd" in names and "b2_peer_allreduce" in names
+    assert len(names) >= 20
+
+
+def test_every_declared_symbol_is_exported(lib):
+    cdll = ctypes.CDLL(lib.LIB_PATH)
+    missing = [n for n in declared_symbols() if not hasattr(cdll, n)]
+    assert not missing, f"declared in b2train.h but not exported: {missing}"
+
+
+def test_python_binding_covers_the_header(lib):
+    assert sorted(lib.EXPORTS) == declared_symbols()
+
+
+def test_version_and_sizes(lib):
+    assert lib.lib.b2_version() == 100
+    assert lib.lib.b2_sumsq_scratch_bytes() >= 4 * (32 + 148)
+    assert lib.lib.b2_peer_flags_bytes() == 256
+    assert lib.lib.b2_lmhead_ce_workspace_bytes(8192) == 64 * 8192 * 8
+    assert lib.lib.b2_lmhead_ce_workspace_bytes(1) == 64 * 128 * 8
+
+
+def test_bad_arguments_are_rejected_without_a_gpu(lib):
+    L = lib.lib
+    assert L.b2_adamw(None, None, None, None, 16, 0, 0, 0, 1e-3, 0.9, 0.999, 1e-8, 0.0, 1, None, None) == -1
+    assert b"null" in L.b2_last_error()
+    assert L.b2_adamw(16, 16, 16, 16, 16, 0, 0, 0, 1e-3, 0.9, 0.999, 1e-8, 0.0, 0, None, None) == -1
+    assert b"step" in L.b2_last_error()
+    assert L.b2_adamw(16, 16, 16, 16, 16, 7, 0, 0, 1e-3, 0.9, 0.999, 1e-8, 0.0, 1, None, None) == -1
+    assert L.b2_adamw(8, 16, 16, 16, 16, 0, 0, 0, 1e-3, 0.9, 0.999, 1e-8, 0.0, 1, None, None) == -1
+    assert b"aligned" in L.b2_last_error()
+    assert L.b2_sumsq(16, 8, 3, 16, 16, 0, None) == -1
+    assert L.b2_ce_rows_fwd(16, 0, 4, 0, 0, 16, 0, -100, 16, 16, 16, 16, None, None) == -1
+    assert L.b2_lmhead_ce_fwd(16, 8, 16, 8, None, 16, 10, 8, 8, 3, -100, 1, 16, 0, 16, 16, 16, 16, None, None) == -1
+    assert b"multiple of shift_T" in L.b2_last_error()
+    assert L.b2_peer_allreduce(None, None, 9, 0, 0, 64, 1, 0.5, 1, 0, 0, None) == -1
+    assert L.b2_peer_allreduce(None, None, 2, 2, 0, 64, 1, 0.5, 1, 0, 0, None) == -1
+    with pytest.raises(lib.B2Error):
+        lib.call("b2_scale", None, 8, 0, None, None)
+
+
+def test_peer_slices_partition_the_buffer(lib):
+    b, e = ctypes.c_size_t(), ctypes.c_size_t()
+    for dtype, per_vec in ((0, 4), (1, 8)):
+        for n in (per_vec, 64, 1 << 20, (1 << 20) + 64, 7 * 64):
+            for world in (1, 2, 3, 4, 8):
+                cover = []
+                for r in range(world):
+                    assert lib.lib.b2_peer_slice(n, dtype, world, r, ctypes.byref(b), ctypes.byref(e)) == 0
+                    assert b.value % per_vec == 0 and b.value <= e.value <= n
+                    cover.append((b.value, e.value))
+                assert cover[0][0] == 0 and cover[-1][1] == n
+                assert all(cover[i][1] == cover[i + 1][0] for i in range(world - 1))
+
+
+def test_no_cpu_fallback(lib):
+    import torch
+    from b200_train import ops
+    x = torch.zeros(64)
+    with pytest.raises(lib.B2Error):
+        ops.sumsq(x)
+    with pytest.raises(lib.B2Error):
+        ops.adamw_(x, x, x.clone(), x.clone(), lr=1e-3, step=1)

@@ -1,0 +1,162 @@
+"""Host-side logic that needs no GPU: flat storage, optimizer bookkeeping, the ray.train-shaped trainer shim with
+a world_size-2 gloo run (the reference's use_gpu=False path), data-loader sharding."""
+import os
+import tempfile
+
+import numpy as np
+import pytest
+import torch
+import torch.nn as nn
+
+
+def test_flatten_keeps_parameters_and_values():
+    from b200_train.flat import ALIGN, buffers_of, flatten_params
+    torch.manual_seed(0)
+    m = nn.Sequential(nn.Linear(5, 7), nn.LayerNorm(7), nn.Linear(7, 3))
+    before = {n: p.detach().clone() for n, p in m.named_parameters()}
+    ids = [id(p) for p in m.parameters()]
+    bufs = flatten_params(list(m.parameters()))
+    assert len(bufs) == 1 and bufs[0].numel % ALIGN == 0
+    assert [id(p) for p in m.parameters()] == ids                       # same Parameter objects
+    for n, p in m.named_parameters():
+        assert torch.equal(p, before[n])
+        assert p.grad is not None and p.grad.shape == p.shape and float(p.grad.abs().sum()) == 0.0
+        assert p._b2_flat[1] % ALIGN == 0
+    # autograd accumulates into the flat gradient buffer in place
+    m(torch.randn(4, 5)).sum().backward()
+    buf = bufs[0]
+    assert float(buf.grad.abs().sum()) > 0
+    for i, p in enumerate(buf.params):
+        assert p.grad.data_ptr() == buf.grad_view(i).data_ptr()
+    # a dropped .grad is re-installed; a foreign .grad is adopted by copy
+    p0 = buf.params[0]
+    p0.grad = torch.ones_like(p0)
+    assert buf.install_grads() == 1 and torch.equal(buf.grad_view(0), torch.ones_like(p0))
+    again = flatten_params(list(m.parameters()))
+    assert again == bufs                                                # idempotent
+    assert buffers_of(list(m.parameters()))[0] == bufs
+
+
+def test_tied_weights_are_flattened_once():
+    from b200_train.flat import flatten_params
+    emb = nn.Embedding(11, 4)
+    head = nn.Linear(4, 11, bias=False)
+    head.weight = emb.weight
+    bufs = flatten_params(list(emb.parameters()) + list(head.parameters()))
+    assert len(bufs[0].params) == 1 and head.weight is emb.weight
+
+
+def test_adamw_bookkeeping_matches_torch_layout():
+    import b200_train
+    m = nn.Sequential(nn.Linear(6, 6), nn.LayerNorm(6))
+    decay = [m[0].weight]
+    no_decay = [m[0].bias, m[1].weight, m[1].bias]
+    opt = b200_train.AdamW([{"params": decay, "weight_decay": 0.1}, {"params": no_decay, "weight_decay": 0.0}], lr=1e-3)
+    ref = torch.optim.AdamW([{"params": [p.detach().clone().requires_grad_() for p in decay], "weight_decay": 0.1},
+                             {"params": [p.detach().clone().requires_grad_() for p in no_decay], "weight_decay": 0.0}],
+                            lr=1e-3)
+    assert [set(g) - {"params"} for g in opt.param_groups] == [set(g) - {"params"} for g in ref.param_groups] or \
+        all(k in opt.param_groups[0] for k in ("lr", "betas", "eps", "weight_decay"))
+    bufs = opt.flat_buffers()
+    table = opt._chunk_group[id(bufs[0])]
+    buf = bufs[0]
+    for p, o in zip(buf.params, buf.offsets):
+        want = 0 if any(p is q for q in decay) else 1
+        assert int(table[o // 64]) == want
+    sd = opt.state_dict()
+    assert set(sd["state"][0]) == {"step", "exp_avg", "exp_avg_sq"}
+    assert sd["state"][0]["exp_avg"].shape == m[0].weight.shape
+    # LambdaLR drives group["lr"] exactly as with torch's optimizer
+    sched = torch.optim.lr_scheduler.LambdaLR(opt, lambda s: 0.5)
+    assert opt.param_groups[0]["lr"] == pytest.approx(5e-4)
+    # there is no CPU arithmetic behind step(): it must fail loudly, not fall back
+    m(torch.randn(2, 6)).sum().backward()
+    with pytest.raises(b200_train.B2Error):
+        opt.step()
+    with pytest.raises(b200_train.B2Error):
+        b200_train.AdamW(m.parameters(), amsgrad=True)
+    with pytest.raises(ValueError):
+        b200_train.AdamW(m.parameters(), lr=-1.0)
+
+
+def test_loss_modules_refuse_cpu_tensors():
+    import b200_train
+    crit = b200_train.CrossEntropyLoss()
+    with pytest.raises(b200_train.B2Error):
+        crit(torch.randn(4, 5), torch.tensor([0, 1, 2, 3]))
+    with pytest.raises(b200_train.B2Error):
+        b200_train.CrossEntropyLoss(label_smoothing=0.1)
+    with pytest.raises(b200_train.B2Error):
+        b200_train.fused_lm_head_ce(torch.randn(2, 3, 8), torch.randn(10, 8), torch.zeros(2, 3, dtype=torch.long))
+
+
+def test_prepare_model_single_worker_returns_bare_module():
+    import b200_train
+    m = nn.Linear(3, 3)
+    out = b200_train.prepare_model(m, move_to_device=False)
+    assert out is m and not hasattr(out, "module")        # same as Ray with world_size == 1
+
+
+def _cpu_loop(config):
+    """Shape of the reference's train_loop_per_worker (ref: pytorch_llm_ray.py:122-313) on the use_gpu=False path."""
+    import torch.distributed as dist
+    from b200_train import train
+    from oracle import torch_ref as TR
+    ctx = train.get_context()
+    rank, world = ctx.get_world_rank(), ctx.get_world_size()
+    assert train.torch.get_device().type == "cpu"
+    torch.set_num_threads(1)
+    torch.manual_seed(100 + rank)                          # ranks start DIFFERENT: DDP must sync rank 0's weights
+    V = 37
+    model = TR.disable_dropout(TR.BasicLLMRestated(V, embed_dim=32, num_heads=2, num_layers=1, hidden_dim=64, max_seq_len=64))
+    model = train.torch.prepare_model(model)
+    assert hasattr(model, "module")
+    opt = torch.optim.AdamW(model.parameters(), lr=config["lr"], weight_decay=0.01)
+    crit = nn.CrossEntropyLoss()
+    stream = TR.synthetic_char_stream(2000, V)
+    ds = torch.utils.data.TensorDataset(*TR.windows(stream, torch.arange(64), 16))
+    dl = train.torch.prepare_data_loader(torch.utils.data.DataLoader(ds, batch_size=4, shuffle=True, drop_last=True))
+    assert len(dl) == 64 // world // 4
+    dl.sampler.set_epoch(0)
+    for step, (x, y) in enumerate(dl):
+        loss, _ = TR.basic_llm_step(model, opt, None, crit, x, y, V, 1.0)
+        if step == 2:
+            break
+    checksum = torch.stack([p.detach().double().sum() for p in model.parameters()]).sum().reshape(1)
+    both = [torch.zeros(1, dtype=torch.float64) for _ in range(world)]
+    dist.all_gather(both, checksum)
+    assert all(torch.equal(both[0], b) for b in both), "ranks diverged"
+    ckpt = None
+    if rank == 0:
+        d = tempfile.mkdtemp()
+        torch.save(model.module.state_dict(), os.path.join(d, "model.pth"))
+        ckpt = train.Checkpoint.from_directory(d)
+    train.report({"loss": float(loss), "checksum": float(checksum)}, checkpoint=ckpt)
+
+
+def test_trainer_shim_two_gloo_workers(tmp_path):
+    from b200_train.train import CheckpointConfig, RunConfig, ScalingConfig, TorchConfig, TorchTrainer
+    trainer = TorchTrainer(_cpu_loop, train_loop_config={"lr": 3e-4},
+                           scaling_config=ScalingConfig(num_workers=2, use_gpu=False),
+                           run_config=RunConfig(name="t", storage_path=str(tmp_path),
+                                                checkpoint_config=CheckpointConfig(num_to_keep=1,
+                                                                                   checkpoint_score_attribute="loss",
+                                                                                   checkpoint_score_order="min")),
+                           torch_config=TorchConfig(backend="gloo"))
+    result = trainer.fit()
+    assert result.error is None
+    assert np.isfinite(result.metrics["loss"]) and "checksum" in result.metrics
+    assert result.checkpoint is not None and os.path.exists(os.path.join(result.checkpoint.path, "model.pth"))
+
+
+def test_trainer_shim_single_worker_inline():
+    from b200_train import train
+    seen = {}
+
+    def loop(cfg):
+        ctx = train.get_context()
+        seen["rank"], seen["world"], seen["cfg"] = ctx.get_world_rank(), ctx.get_world_size(), cfg
+        train.report({"loss": 1.5})
+
+    r = train.TorchTrainer(loop, train_loop_config={"a": 1}, scaling_config=train.ScalingConfig(num_workers=1)).fit()
+    assert seen == {"rank": 0, "world": 1, "cfg": {"a": 1}} and r.metrics == {"loss": 1.5}

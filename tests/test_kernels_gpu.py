@@ -244,12 +244,14 @@ def test_adamw_bf16_params(ops, state_dtype):
     # exact-arithmetic result, rounded once: the kernel must be within 1 bf16 ulp of it (and so is torch's
     # op-by-op bf16 path, which the oracle models with state_bf16=True)
     pe, me, ve = O.adamw_step(p, g, m0, v0, step=1, state_bf16=False, **hp)
-    assert (np.abs(pt.float().cpu().numpy() - pe) <= O.bf16_ulp(pe)).all()
+    assert (np.abs(pt.float().cpu().numpy() - pe) <= O.bf16_ulp(np.maximum(np.abs(pe), np.abs(p)))).all()
     if state_dtype == torch.bfloat16:
         po, mo, vo = O.adamw_step(p, g, m0, v0, step=1, state_bf16=True, **hp)
         assert (np.abs(mt.float().cpu().numpy() - mo) <= O.bf16_ulp(mo) + 1e-38).all()
         assert (np.abs(vt.float().cpu().numpy() - vo) <= O.bf16_ulp(vo) + 1e-38).all()
-        assert (np.abs(pt.float().cpu().numpy() - po) <= O.bf16_ulp(po)).all()
+        # 1 bf16 ulp at the magnitude of the operands (an update that crosses zero cancels, so the ulp of the
+        # tiny result is not the right yardstick)
+        assert (np.abs(pt.float().cpu().numpy() - po) <= O.bf16_ulp(np.maximum(np.abs(po), np.abs(p)))).all()
     else:
         np.testing.assert_allclose(mt.cpu().numpy(), me, rtol=1e-6, atol=1e-12)
         np.testing.assert_allclose(vt.cpu().numpy(), ve, rtol=1e-6, atol=1e-16)
