@@ -1,0 +1,302 @@
+#!/usr/bin/env python
+"""bench.py — train tokens/sec of the data-parallel step on N B200s of one box (BASELINE.json metric).
+
+    python bench.py --gpus 1 --steps K --warmup W                 (N>1: launched by torch.distributed.run, one rank/GPU)
+    python bench.py --impl reference --gpus N --steps K --warmup W   (the reference's CPU path on the host cores)
+
+Workload (config.workload): BASELINE configs[1] — GPT-2 small (124M, random init from GPT2Config()), full fine-tune,
+seq 1024, bf16 parameters/gradients/AdamW state (the reference's full-FT dtype regime), 8 sequences
+per GPU per step, synthetic wikitext-2-shaped token batches with a -100 padded tail. One step = forward (stock HF
+backbone) -> fused LM-head+cross-entropy (tcgen05) -> backward -> [N>1: peer-memory gradient all-reduce] ->
+clip_grad_norm_(0.3) -> fused AdamW(lr 2e-4, wd 1e-3), i.e. the reference's step tail with our three kernels in it.
+Weak scaling: the per-GPU batch is fixed as N grows.
+
+Prints ONE JSON line (rank 0). `value` = tokens/s with the batch already resident in HBM; `e2e` = the same step
+driven through the public API from pinned host buffers, H2D copy and loss D2H inside the timed region.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import tempfile
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "gke-ray-train_b200"))
+
+B_PER_GPU, SEQ, MAX_NORM, LR, WD = 8, 1024, 0.3, 2e-4, 1e-3
+METRIC = "train tokens/sec/box"
+
+
+def load_peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        with open(p) as f:
+            d = json.load(f)
+        return dict(hbm_gbs=d["hbm_gbs"], bf16_tflops=d["bf16_tflops"], bf16_tflops_sustained=d.get("bf16_tflops_sustained"),
+                    source="measured (MEASURED_PEAKS.json)")
+    return dict(hbm_gbs=6650.0, bf16_tflops=1590.0, bf16_tflops_sustained=1400.0, source="fallback (B200_PROFILING.md)")
+
+
+class ClockSampler:
+    """Samples SM clocks and throttle reasons with nvidia-smi while the timed region runs."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index=0):
+        self.path = tempfile.mktemp(prefix="b2_clocks_")
+        self.proc = None
+        self.index = index
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}",
+                                          "--format=csv,noheader,nounits", "-lms", "50"],
+                                         stdout=open(self.path, "w"), stderr=subprocess.DEVNULL)
+        except OSError:
+            self.proc = None
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except subprocess.TimeoutExpired:
+            self.proc.kill()
+        rows = []
+        with open(self.path) as f:
+            for line in f:
+                parts = [x.strip() for x in line.split(",")]
+                if len(parts) >= 7:
+                    rows.append(parts)
+        os.unlink(self.path)
+        if not rows:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["no samples"]}
+        sm = sorted(float(r[0]) for r in rows if r[0].replace(".", "").isdigit())
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = [n for i, n in enumerate(names) if any(r[3 + i].lower().startswith("active") for r in rows)]
+        pw = [float(r[2]) for r in rows if r[2].replace(".", "").isdigit()]
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": float(rows[0][1]) if rows[0][1].replace(".", "").isdigit() else None,
+                "reasons": reasons, "samples": len(rows), "power_w_max": max(pw) if pw else None}
+
+
+# ------------------------------------------------------------------------------------------------ reference arm
+def run_reference(args):
+    """The reference's own CPU implementation of the path (stock torch/transformers call sequence, oracle/torch_ref.py)
+    on the box's host cores, all threads, on a bounded sample of the same workload."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    import torch
+    from oracle import torch_ref as TR
+    torch.set_num_threads(os.cpu_count() or 1)
+    steps = max(1, min(args.steps, 3))
+    warm = max(1, min(args.warmup, 1))
+    r = TR.cpu_gpt2_baseline(steps=steps, warmup=warm, B=1, T=SEQ, dtype=torch.bfloat16)
+    line = {
+        "impl": "reference", "metric": METRIC, "value": r["tokens_per_s"], "unit": "tokens/s", "n_gpus": args.gpus,
+        "steps": steps, "warmup": warm, "ms_per_step": r["ms_per_step"], "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
+        "config": {"workload": "gpt2-124m full fine-tune, seq 1024, bf16 (BASELINE configs[1])",
+                   "note": "reference = stock torch/transformers step (HF loss, clip_grad_norm_, torch.optim.AdamW) on host cores; "
+                           "bounded sample; ray/trl/accelerate are not installed so the loop body is restated in oracle/torch_ref.py"},
+        "cpu_baseline": {"value": r["tokens_per_s"], "unit": "tokens/s", "cores": r["threads"], "kind": "port", "sample": r["sample"]},
+        "e2e": {"value": r["tokens_per_s"], "unit": "tokens/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+# ------------------------------------------------------------------------------------------------ our arm
+def f1_roofline(torch, b200, model, device, peaks, iters=5):
+    """Times the fused LM-head+CE kernel family (forward + backward: 4 launches of the tcgen05 mainloop) alone, with CUDA
+    events on the launching stream and an L2 flush between iterations. Algorithmic flops = 6*N*V*D."""
+    W = model.get_output_embeddings().weight
+    V, D = W.shape
+    N = B_PER_GPU * SEQ
+    g = torch.Generator(device="cpu").manual_seed(7)
+    H = (torch.randn(N, D, generator=g) * 0.5).to(device, torch.bfloat16).requires_grad_(True)
+    Wl = W.detach().clone().requires_grad_(True)
+    labels = torch.randint(0, V, (B_PER_GPU, SEQ), generator=g).to(device)
+    flush = torch.empty(256 * 1024 * 1024, dtype=torch.uint8, device=device)
+    times = []
+    for it in range(iters + 2):
+        flush.fill_(it & 0xff)
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        loss = b200.fused_lm_head_ce(H.view(B_PER_GPU, SEQ, D), Wl, labels)
+        loss.backward()
+        e1.record()
+        torch.cuda.synchronize()
+        H.grad = None
+        Wl.grad = None
+        if it >= 2:
+            times.append(e0.elapsed_time(e1))
+    ms = sum(times) / len(times)
+    flops = 6.0 * N * V * D
+    achieved = flops / (ms * 1e-3) / 1e12
+    return {"bound": "tensor", "achieved": achieved, "peak": peaks["bf16_tflops"], "unit": "TFLOP/s",
+            "frac": achieved / peaks["bf16_tflops"], "traffic": None,
+            "kernel": "umma_kernel (fused LM-head+CE fwd, dlogits recompute, dH and dW GEMMs)",
+            "ms": ms, "algorithmic_flops": flops, "peak_source": peaks["source"] + ", burst bf16 GEMM"}
+
+
+def f3_roofline(torch, ops, device, peaks, n=1 << 27, iters=5):
+    """Fused AdamW alone on a flat pure-bf16 buffer larger than L2 (14 B/element algorithmic)."""
+    p = torch.randn(n, device=device).to(torch.bfloat16)
+    g = (torch.randn(n, device=device) * 0.01).to(torch.bfloat16)
+    m = torch.zeros(n, dtype=torch.bfloat16, device=device)
+    v = torch.zeros(n, dtype=torch.bfloat16, device=device)
+    times = []
+    for it in range(iters + 2):
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        ops.adamw_(p, g, m, v, lr=LR, weight_decay=WD, step=it + 1)
+        e1.record()
+        torch.cuda.synchronize()
+        if it >= 2:
+            times.append(e0.elapsed_time(e1))
+    ms = sum(times) / len(times)
+    gbs = 14.0 * n / (ms * 1e-3) / 1e9
+    return {"bound": "hbm", "achieved": gbs, "peak": peaks["hbm_gbs"], "unit": "GB/s", "frac": gbs / peaks["hbm_gbs"],
+            "traffic": None, "kernel": "adamw_kernel (pure bf16, n=2^27)", "ms": ms}
+
+
+def run_ours(args):
+    import torch
+    import torch.distributed as dist
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device: the product path has no CPU fallback")
+    device = torch.device("cuda", local_rank)
+    torch.cuda.set_device(device)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=device)
+    import b200_train as b200
+    from b200_train import _lib, ops
+    from oracle import torch_ref as TR       # model factory + synthetic data only (shared with the reference arm)
+
+    peaks = load_peaks()
+    model = TR.make_gpt2(dtype=torch.bfloat16, seed=0)
+    model.train()
+    b200.patch_causal_lm(model)
+    model = b200.prepare_model(model)                       # .to(device); peer-memory DDP when world > 1
+    inner = model.module if hasattr(model, "module") else model
+    V = inner.config.vocab_size
+    optimizer = b200.AdamW(TR.hf_param_groups(inner, WD), lr=LR)
+
+    n_batches = 4
+    host = [TR.synthetic_hf_batch(B_PER_GPU, SEQ, V, 1234 + 97 * rank + i) for i in range(n_batches)]
+    pinned = [(a.pin_memory(), b.pin_memory()) for a, b in host]
+    resident = [(a.to(device), b.to(device)) for a, b in host]
+
+    def step(ids, labels):
+        optimizer.zero_grad(set_to_none=True)
+        loss = model(input_ids=ids, labels=labels).loss
+        loss.backward()
+        b200.clip_grad_norm_(model.parameters(), MAX_NORM)
+        optimizer.step()
+        return loss
+
+    def timed(batches_on_host):
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        l0 = _lib.launch_count
+        e0.record()
+        last = None
+        for s in range(args.steps):
+            if batches_on_host:
+                a, b = pinned[s % n_batches]
+                ids, lab = a.to(device, non_blocking=True), b.to(device, non_blocking=True)
+                last = float(step(ids, lab).item())          # D2H of the step's loss, every step
+            else:
+                ids, lab = resident[s % n_batches]
+                last = step(ids, lab)
+        e1.record()
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        ms = torch.tensor([e0.elapsed_time(e1)], device=device)
+        if world > 1:
+            dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        return float(ms.item()), _lib.launch_count - l0, (last if isinstance(last, float) else float(last.item()))
+
+    for s in range(max(args.warmup, 3)):
+        step(*resident[s % n_batches])
+    torch.cuda.synchronize()
+
+    sampler = ClockSampler(local_rank) if rank == 0 else None
+    if sampler:
+        sampler.start()
+    ms_total, launches, last_loss = timed(False)
+    ms_e2e, _, _ = timed(True)
+    clocks = sampler.stop() if sampler else None      # sampled across both timed regions
+
+    tokens_per_step = world * B_PER_GPU * SEQ
+    value = tokens_per_step * args.steps / (ms_total * 1e-3)
+    e2e = tokens_per_step * args.steps / (ms_e2e * 1e-3)
+
+    roof = cpu = extra = None
+    if rank == 0:
+        roof = f1_roofline(torch, b200, inner, device, peaks)
+        extra = [f3_roofline(torch, ops, device, peaks)]
+    if world > 1:
+        dist.barrier()
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        torch.set_num_threads(os.cpu_count() or 1)
+        r = TR.cpu_gpt2_baseline(steps=2, warmup=1, B=1, T=SEQ, dtype=torch.bfloat16)
+        cpu = {"value": r["tokens_per_s"], "unit": "tokens/s", "cores": r["threads"], "kind": "port", "sample": r["sample"]}
+    if rank == 0:
+        line = {
+            "metric": METRIC, "value": value, "unit": "tokens/s", "n_gpus": world, "steps": args.steps,
+            "warmup": max(args.warmup, 3), "ms_per_step": ms_total / args.steps, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
+            "config": {"workload": "gpt2-124m full fine-tune, seq 1024, bf16 (BASELINE configs[1])",
+                       "global_batch": world * B_PER_GPU, "seq_len": SEQ, "parallelism": f"dp{world}",
+                       "optimizer": "AdamW lr 2e-4 wd 1e-3, clip 0.3, pure-bf16 state",
+                       "l2": "no explicit flush between steps: one step streams params+grads+AdamW state (1.0 GB) and >4 GB of "
+                             "activations, far beyond the 126 MB L2; the roofline micro-runs flush 256 MB between iterations",
+                       "last_loss": last_loss},
+            "e2e": {"value": e2e, "unit": "tokens/s", "h2d_bytes_per_step": 2 * B_PER_GPU * SEQ * 8, "d2h_bytes_per_step": 4,
+                    "ms_per_step": ms_e2e / args.steps},
+            "gpu_launches": launches, "clocks": clocks, "roofline": roof, "rooflines_other": extra, "cpu_baseline": cpu,
+        }
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.barrier()
+        if hasattr(model, "close"):
+            model.close()
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        return run_reference(args)
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    if args.gpus > 1 and world == 1:
+        # convenience: re-launch ourselves one rank per GPU
+        cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={args.gpus}",
+               "--master-addr", "127.0.0.1", "--master-port", "29517", os.path.abspath(__file__), "--gpus", str(args.gpus),
+               "--steps", str(args.steps), "--warmup", str(args.warmup)] + (["--no-cpu-baseline"] if args.no_cpu_baseline else [])
+        raise SystemExit(subprocess.call(cmd))
+    run_ours(args)
+
+
+if __name__ == "__main__":
+    main()

@@ -45,6 +45,8 @@ class AdamW(torch.optim.Optimizer):
         self._buffers = None
         self._chunk_group = {}
         self._group_step = []      # one shared CPU step tensor per param_group (torch keeps one per parameter)
+        if all(p.is_cuda for g in self.param_groups for p in g["params"]):
+            self._setup()           # flatten now, so the very first backward already accumulates into the flat buffer
 
     # ------------------------------------------------------------------ set-up (first step)
     def _setup(self):

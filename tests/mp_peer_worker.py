@@ -1,0 +1,108 @@
+"""Worker for tests/test_multigpu.py — one process per GPU (launched by torch.distributed.run).
+
+Checks, on real peers over NVLink:
+  1. b2_peer_allreduce on a symmetric flat buffer == mean of the ranks' inputs (bit-identical on all ranks; equal to
+     NCCL all_reduce(SUM)/W for W = 2), with the fused sum of squares;
+  2. reduce-scatter + all-gather halves;
+  3. prepare_model + AdamW + clip on a tiny GPT-2: every rank ends with identical parameters, equal (to bf16 tolerance)
+     to a single-process run over the concatenated batch with the stock path.
+Prints 'MP_OK' from rank 0 when everything passed.
+"""
+import os
+import sys
+
+import numpy as np
+import torch
+import torch.distributed as dist
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "gke-ray-train_b200"))
+
+
+def main():
+    rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
+    dev = torch.device("cuda", local)
+    torch.cuda.set_device(dev)
+    dist.init_process_group("nccl", device_id=dev)
+    import b200_train as b200
+    from b200_train.symm import PeerComm
+    from oracle import step_tail as O
+    from oracle import torch_ref as TR
+
+    comm = PeerComm(dev)
+    for dtype in (torch.bfloat16, torch.float32):
+        n = 64 * 4099
+        t = comm.alloc(n, dtype, dev)
+        g = torch.Generator(device="cpu").manual_seed(100 + rank)
+        src = (torch.randn(n, generator=g) * 0.1).to(dev, dtype)
+        for it in range(3):                                  # repeated calls exercise the epoch flags
+            t.copy_(src)
+            ref = src.float().clone()
+            dist.all_reduce(ref)                             # NCCL, checker only
+            want = (ref * np.float32(1.0 / world)).to(dtype)
+            parts = comm.allreduce_(t, want_sumsq=True)
+            torch.cuda.synchronize()
+            tol = 0 if (world == 2 or dtype == torch.float32) else float(want.float().abs().max()) * 2 ** -7
+            if dtype == torch.float32 and world > 2:
+                tol = 1e-6                                    # different fp32 summation order than NCCL's ring
+            assert (t.float() - want.float()).abs().max() <= tol, (dtype, it, (t.float() - want.float()).abs().max())
+            bits = t.view(torch.int16 if dtype == torch.bfloat16 else torch.int32).clone()
+            b0 = bits.clone()
+            dist.broadcast(b0, 0)
+            assert torch.equal(bits, b0), "ranks hold different bits after the peer all-reduce"
+            np.testing.assert_allclose(float(parts.sum().item()), t.float().double().pow(2).sum().item(), rtol=1e-5)
+        # reduce-scatter, then all-gather
+        t.copy_(src)
+        comm.allreduce_(t, scatter_only=True)
+        comm.allgather_(t)
+        torch.cuda.synchronize()
+        dist.barrier()
+        assert (t.float() - want.float()).abs().max() <= tol
+
+    # --- prepare_model path on a tiny GPT-2
+    kw = dict(dtype=torch.bfloat16, seed=0, vocab_size=2003, n_embd=128, n_layer=2, n_head=4, n_positions=64,
+              resid_pdrop=0.0, embd_pdrop=0.0, attn_pdrop=0.0)
+    torch.manual_seed(1000 + rank)                           # ranks start different; prepare_model syncs rank 0's weights
+    model = TR.make_gpt2(**{**kw, "seed": rank}).train()
+    b200.patch_causal_lm(model)
+    model = b200.prepare_model(model)
+    assert hasattr(model, "module")
+    opt = b200.AdamW(TR.hf_param_groups(model.module, 1e-3), lr=2e-4)
+    batches = [TR.synthetic_hf_batch(4, 64, 2003, seed=50 + r, device=dev) for r in range(world)]
+    for step in range(2):
+        opt.zero_grad(set_to_none=True)
+        ids, lab = batches[rank]
+        loss = model(input_ids=ids, labels=lab).loss
+        loss.backward()
+        norm = b200.clip_grad_norm_(model.parameters(), 0.3)
+        opt.step()
+    flat = torch.cat([p.detach().float().reshape(-1) for p in model.parameters()])
+    f0 = flat.clone()
+    dist.broadcast(f0, 0)
+    assert torch.equal(flat, f0), "parameters diverged across ranks"
+    # stock single-process equivalent: DDP averages per-rank mean losses -> emulate by averaging gradients
+    ref = TR.make_gpt2(**kw).to(dev).train()
+    ropt = torch.optim.AdamW(TR.hf_param_groups(ref, 1e-3), lr=2e-4)
+    before = [p.detach().clone() for p in ref.parameters()]
+    for step in range(2):
+        ropt.zero_grad(set_to_none=True)
+        for ids, lab in batches:
+            (ref(input_ids=ids, labels=lab).loss / world).backward()
+        torch.nn.utils.clip_grad_norm_(ref.parameters(), 0.3)
+        ropt.step()
+    for (n, a), b, b4 in zip(model.module.named_parameters(), ref.parameters(), before):
+        got, want = a.detach().float().cpu().numpy(), b.detach().float().cpu().numpy()
+        ulp = O.bf16_ulp(np.maximum(np.abs(want), np.abs(b4.float().cpu().numpy())))
+        err = np.abs(got - want)
+        assert (err <= 2 * ulp).all() and (err > ulp).mean() < 2e-3, (n, err.max())
+    dist.barrier()
+    model.close()
+    comm.close()
+    if rank == 0:
+        print("MP_OK", flush=True)
+    dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

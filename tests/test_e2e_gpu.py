@@ -1,0 +1,280 @@
+"""End-to-end parity on the GPU: the drop-in surface (prepare_model / CrossEntropyLoss / fused LM-head loss /
+clip_grad_norm_ / AdamW) against the reference's stock call sequence (oracle/torch_ref.py), the committed golden
+fixtures, and size-independent properties at BASELINE.json's full sizes.
+
+Stated tolerances: masking / token counts bit-exact; fp32 path — loss rtol 1e-5, parameters atol 2e-6 after 3 steps;
+bf16 path — loss atol 5e-3, parameters within 2 bf16 ulp (at operand magnitude) with fewer than 0.1 % of elements
+off by more than 1 ulp.
+"""
+import copy
+import ctypes
+import os
+
+import numpy as np
+import pytest
+import torch
+import torch.nn as nn
+
+from oracle import step_tail as O
+from oracle import torch_ref as TR
+
+pytestmark = pytest.mark.gpu
+G = os.path.join(os.path.dirname(__file__), "golden")
+
+
+def dev():
+    return torch.device("cuda", 0)
+
+
+@pytest.fixture(scope="module")
+def b200():
+    import b200_train
+    return b200_train
+
+
+# ------------------------------------------------------------------------------------------ golden fixtures
+def test_golden_basicllm_head_loss(b200):
+    """features/fc_out of the reference's own BasicLLM -> our CrossEntropyLoss == the reference model's loss."""
+    g = np.load(os.path.join(G, "basicllm_tiny.npz"))
+    H = torch.from_numpy(g["features"]).to(dev()).reshape(-1, 32)
+    logits = torch.nn.functional.linear(H, torch.from_numpy(g["fc_w"]).to(dev()), torch.from_numpy(g["fc_b"]).to(dev()))
+    y = torch.from_numpy(g["y"]).to(dev()).reshape(-1)
+    loss = b200.CrossEntropyLoss()(logits, y)
+    np.testing.assert_allclose(loss.item(), g["loss0"], rtol=1e-5)
+
+
+def test_golden_hf_tiny_gpt2_fused_loss_and_grads(b200):
+    g = np.load(os.path.join(G, "hf_tiny_gpt2.npz"))
+    H = torch.from_numpy(g["hidden"]).to(dev()).to(torch.bfloat16).requires_grad_(True)
+    W = torch.from_numpy(g["W"]).to(dev()).to(torch.bfloat16).requires_grad_(True)
+    labels = torch.from_numpy(g["labels"]).to(dev())
+    loss = b200.fused_lm_head_ce(H, W, labels)
+    loss.backward()
+    np.testing.assert_allclose(loss.item(), g["loss"], rtol=0, atol=2e-3)
+    from b200_train import ops
+    r = ops.lmhead_ce_fwd(H.detach().reshape(-1, 64), W.detach(), labels.reshape(-1), shift_T=labels.shape[1])
+    assert int(r.n_valid.item()) == int(g["n_valid"])
+    for got, want in ((H.grad.float().cpu().numpy(), g["dH"]), (W.grad.float().cpu().numpy(), g["dW"])):
+        err = np.abs(got - want)
+        assert (err <= 2 * O.bf16_ulp(want) + 2e-6).mean() > 0.999
+        assert err.max() <= 8 * O.bf16_ulp(np.abs(want).max())
+
+
+# ------------------------------------------------------------------------------------------ BasicLLM loop, fp32
+def test_basicllm_fp32_three_steps_match_reference_loop(b200):
+    V = 283
+    torch.manual_seed(0)
+    ref_model = TR.disable_dropout(TR.BasicLLMRestated(V, embed_dim=64, num_heads=4, num_layers=2, hidden_dim=128,
+                                                       max_seq_len=128)).to(dev())
+    my_model = copy.deepcopy(ref_model)
+    my_model = b200.prepare_model(my_model)                         # world 1: bare module, as with Ray
+    assert my_model is not None and not hasattr(my_model, "module")
+    ref_opt = torch.optim.AdamW(ref_model.parameters(), lr=3e-4, weight_decay=0.01)
+    my_opt = b200.AdamW(my_model.parameters(), lr=3e-4, weight_decay=0.01)
+    ref_sched = torch.optim.lr_scheduler.LambdaLR(ref_opt, TR.lr_lambda_factory(20))
+    my_sched = torch.optim.lr_scheduler.LambdaLR(my_opt, TR.lr_lambda_factory(20))
+    ref_crit, my_crit = nn.CrossEntropyLoss(), b200.CrossEntropyLoss()
+    stream = TR.synthetic_char_stream(4000, V).to(dev())
+    for s in range(3):
+        idx = torch.arange(8, device=dev()) * 37 + s
+        ar = torch.arange(32, device=dev())
+        x, y = stream[idx[:, None] + ar], stream[idx[:, None] + ar + 1]
+        l_ref, n_ref = TR.basic_llm_step(ref_model, ref_opt, ref_sched, ref_crit, x, y, V, 1.0)
+        # the reference's loop body (ref :272-279) with our drop-ins
+        my_opt.zero_grad(set_to_none=True)
+        out = my_model(x)
+        loss = my_crit(out.reshape(-1, V), y.reshape(-1))
+        loss.backward()
+        n_my = b200.clip_grad_norm_(my_model.parameters(), max_norm=1.0)
+        my_opt.step()
+        my_sched.step()
+        np.testing.assert_allclose(loss.item(), l_ref.item(), rtol=1e-5)
+        np.testing.assert_allclose(n_my.item(), n_ref.item(), rtol=1e-4)
+    for (n, a), (_, b) in zip(my_model.named_parameters(), ref_model.named_parameters()):
+        # Elements whose gradient is mathematically zero (e.g. the key bias of attention: soft-max is shift-invariant)
+        # carry only rounding noise, which Adam normalises to +-lr steps of arbitrary sign in ANY implementation; they
+        # are identified by the reference's own second-moment estimate and left out.
+        live = (ref_opt.state[b]["exp_avg_sq"] > 1e-14).cpu().numpy()
+        got, want = a.detach().cpu().numpy(), b.detach().cpu().numpy()
+        np.testing.assert_allclose(got[live], want[live], rtol=0, atol=2e-6, err_msg=n)
+        assert np.abs(got - want).max() <= 3 * 3e-4 * 2 + 1e-6, n
+    # optimizer.state_dict() keeps torch's layout (ref :302 saves it)
+    sd, rd = my_opt.state_dict(), ref_opt.state_dict()
+    assert sd["state"].keys() == rd["state"].keys()
+    for k in rd["state"]:
+        assert float(sd["state"][k]["step"]) == float(rd["state"][k]["step"]) == 3.0
+        np.testing.assert_allclose(sd["state"][k]["exp_avg"].cpu().numpy(), rd["state"][k]["exp_avg"].cpu().numpy(), atol=1e-7)
+
+
+# ------------------------------------------------------------------------------------------ HF causal LM, bf16
+def _tiny_gpt2():
+    return TR.make_gpt2(dtype=torch.bfloat16, seed=0, vocab_size=2003, n_embd=128, n_layer=2, n_head=4, n_positions=64,
+                        resid_pdrop=0.0, embd_pdrop=0.0, attn_pdrop=0.0).to(dev())
+
+
+def _bf16_close(got, want, before, name):
+    got, want, before = (t.detach().float().cpu().numpy() for t in (got, want, before))
+    ulp = O.bf16_ulp(np.maximum(np.abs(want), np.abs(before)))
+    err = np.abs(got - want)
+    assert (err <= 2 * ulp).all(), f"{name}: max err {err.max()} vs ulp {ulp.reshape(-1)[err.argmax()]}"
+    assert (err > ulp).mean() < 1e-3, f"{name}: {(err > ulp).mean():.2e} of elements off by more than 1 bf16 ulp"
+
+
+@pytest.mark.parametrize("micro_batches", [1, 2])
+def test_hf_gpt2_bf16_step_matches_stock(b200, micro_batches):
+    ref_model = _tiny_gpt2().train()
+    my_model = b200.patch_causal_lm(copy.deepcopy(ref_model)).train()
+    before = {n: p.detach().clone() for n, p in ref_model.named_parameters()}
+    ref_opt = torch.optim.AdamW(TR.hf_param_groups(ref_model, 1e-3), lr=2e-4)
+    my_opt = b200.AdamW(TR.hf_param_groups(my_model, 1e-3), lr=2e-4)
+    batches = [TR.synthetic_hf_batch(4, 64, 2003, seed=1234 + i, device=dev()) for i in range(micro_batches)]
+    l_ref, n_ref = TR.hf_causal_lm_step(ref_model, ref_opt, batches, 0.3)
+    # same step with the drop-ins
+    num_items = sum(int((lab[..., 1:] != -100).sum()) for _, lab in batches)
+    my_opt.zero_grad(set_to_none=True)
+    total = 0.0
+    for ids, lab in batches:
+        out = my_model(input_ids=ids, labels=lab, num_items_in_batch=num_items) if micro_batches > 1 \
+            else my_model(input_ids=ids, labels=lab)
+        assert out.logits is None
+        out.loss.backward()
+        total += float(out.loss.item())
+    n_my = b200.clip_grad_norm_(my_model.parameters(), 0.3)
+    my_opt.step()
+    np.testing.assert_allclose(total, float(l_ref), rtol=0, atol=5e-3)
+    np.testing.assert_allclose(n_my.item(), float(n_ref), rtol=2e-2)
+    for (n, a), (_, b) in zip(my_model.named_parameters(), ref_model.named_parameters()):
+        _bf16_close(a, b, before[n], n)
+
+
+def test_patch_causal_lm_llama_shape(b200):
+    """Llama-shaped (untied head, GQA, RMSNorm) model through the same patch: loss equals the stock HF loss."""
+    model = TR.make_llama(dtype=torch.bfloat16, seed=0, vocab_size=4099, hidden_size=128, intermediate_size=256,
+                          num_hidden_layers=2, num_attention_heads=4, num_key_value_heads=2, head_dim=32,
+                          tie_word_embeddings=False, max_position_embeddings=128).to(dev()).train()
+    ids, labels = TR.synthetic_hf_batch(2, 96, 4099, seed=5, device=dev())
+    with torch.no_grad():
+        want = model(input_ids=ids, labels=labels).loss.item()
+    b200.patch_causal_lm(model)
+    out = model(input_ids=ids, labels=labels)
+    np.testing.assert_allclose(out.loss.item(), want, rtol=0, atol=5e-3)
+    out.loss.backward()
+    assert model.lm_head.weight.grad is not None and torch.isfinite(model.lm_head.weight.grad).all()
+
+
+# ------------------------------------------------------------------------------------------ full-size properties
+def test_full_size_lmhead_properties(b200):
+    """BASELINE configs[1] head shape: N = 8*1024 tokens, D = 768, V = 50257 (ragged last tile)."""
+    from b200_train import ops
+    N, D, V, T = 8192, 768, 50257, 1024
+    g = torch.Generator(device="cpu").manual_seed(3)
+    H = (torch.randn(N, D, generator=g) * 0.7).to(dev(), torch.bfloat16)
+    W = (torch.randn(V, D, generator=g) * 0.05).to(dev(), torch.bfloat16)
+    ids, labels = TR.synthetic_hf_batch(N // T, T, V, seed=9, device=dev())
+    y = labels.reshape(-1)
+    full = ops.lmhead_ce_fwd(H, W, y, shift_T=T)
+    # (1) token count is exact
+    assert int(full.n_valid.item()) == int((labels[:, 1:] != -100).sum())
+    # (2) additivity over row blocks (different work decomposition: other split counts, other CTA assignment)
+    parts = [ops.lmhead_ce_fwd(H[a:a + 2048], W, y[a:a + 2048], shift_T=T) for a in range(0, N, 2048)]
+    s = sum(float(p.loss_sum.item()) for p in parts)
+    np.testing.assert_allclose(float(full.loss_sum.item()), s, rtol=2e-6)
+    assert sum(int(p.n_valid.item()) for p in parts) == int(full.n_valid.item())
+    np.testing.assert_array_equal(torch.cat([p.lse[:2048] for p in parts]).cpu().numpy(), full.lse[:N].cpu().numpy())
+    # (3) a vocabulary permutation leaves every row's lse (to fp32 rounding) and the loss unchanged
+    perm = torch.randperm(V, generator=g).to(dev())
+    inv = torch.empty_like(perm); inv[perm] = torch.arange(V, device=dev())
+    yp = torch.where(y >= 0, inv[y.clamp(min=0)], y)
+    permd = ops.lmhead_ce_fwd(H, W[perm].contiguous(), yp, shift_T=T)
+    np.testing.assert_allclose(permd.lse[:N].cpu().numpy(), full.lse[:N].cpu().numpy(), rtol=0, atol=2e-5)
+    np.testing.assert_allclose(float(permd.loss_mean.item()), float(full.loss_mean.item()), rtol=1e-6)
+    # (4) against torch on the same device (bf16 GEMM, fp32 soft-max — the reference's own arithmetic)
+    logits = (H @ W.t()).float()
+    ys = torch.full_like(labels, -100); ys[:, :-1] = labels[:, 1:]
+    want = torch.nn.functional.cross_entropy(logits, ys.reshape(-1), ignore_index=-100)
+    np.testing.assert_allclose(float(full.loss_mean.item()), float(want.item()), rtol=0, atol=2e-3)
+    del logits
+
+
+def test_full_size_lmhead_backward_vs_torch(b200):
+    N, D, V, T = 4096, 768, 50257, 1024
+    g = torch.Generator(device="cpu").manual_seed(4)
+    H0 = (torch.randn(N, D, generator=g) * 0.7).to(dev(), torch.bfloat16)
+    W0 = (torch.randn(V, D, generator=g) * 0.05).to(dev(), torch.bfloat16)
+    _, labels = TR.synthetic_hf_batch(N // T, T, V, seed=10, device=dev())
+    H, W = H0.clone().requires_grad_(True), W0.clone().requires_grad_(True)
+    b200.fused_lm_head_ce(H.view(N // T, T, D), W, labels, chunk_rows=2048).backward()      # 2 chunks: fp32 dW accumulation
+    Hr, Wr = H0.clone().requires_grad_(True), W0.clone().requires_grad_(True)
+    ys = torch.full_like(labels, -100); ys[:, :-1] = labels[:, 1:]
+    torch.nn.functional.cross_entropy((Hr @ Wr.t()).float(), ys.reshape(-1), ignore_index=-100).backward()
+    for got, want, name in ((H.grad, Hr.grad, "dH"), (W.grad, Wr.grad, "dW")):
+        got, want = got.float(), want.float()
+        rel = (got - want).norm() / want.norm()
+        assert rel < 1e-2, f"{name}: relative Frobenius error {rel:.3e}"
+        assert torch.isfinite(got).all()
+    # rows whose label is ignored contribute exactly nothing to dH
+    ign = (ys.reshape(-1) == -100)
+    assert float(H.grad[ign].abs().max()) == 0.0
+
+
+def test_full_size_adamw_and_sumsq_properties(b200):
+    from b200_train import ops
+    n = (1 << 27) + 192
+    g = (torch.randn(n, device=dev()) * 0.01).to(torch.bfloat16)
+    s1 = ops.sumsq(g).item()
+    s2 = ops.sumsq(g * 2).item()                       # exact in bf16: (2g)^2 = 4 g^2
+    np.testing.assert_allclose(s2, 4 * s1, rtol=1e-6)
+    np.testing.assert_allclose(s1, g.float().double().pow(2).sum().item(), rtol=1e-5)
+    p = torch.randn(n, device=dev()).to(torch.bfloat16)
+    p0 = p.clone()
+    m = torch.zeros_like(p); v = torch.zeros_like(p)
+    ops.adamw_(p, g, m, v, lr=0.0, weight_decay=0.0, step=1)     # lr = 0: parameters must come back bit-identical
+    assert torch.equal(p, p0)
+    assert torch.equal(m, (g.float() * np.float32(1.0 - 0.9)).to(torch.bfloat16))
+
+
+# ------------------------------------------------------------------------------------------ F2 on one GPU
+def test_peer_allreduce_single_gpu_emulation(b200):
+    """All `world` ranks' buffers live on one GPU and each rank's kernel runs in turn with the barrier flags already
+    satisfied (kernels that wait for one another must not share a GPU). Slices are independent, so the result equals
+    the real exchange: every buffer ends with round(mean over ranks), plus per-slice sum of squares."""
+    from b200_train import _lib
+    for dtype, world in ((torch.bfloat16, 2), (torch.bfloat16, 8), (torch.float32, 4), (torch.bfloat16, 3)):
+        n = 64 * 1000 + 64
+        rng = torch.Generator(device="cpu").manual_seed(world)
+        bufs = [(torch.randn(n, generator=rng) * 0.1).to(dev(), dtype) for _ in range(world)]
+        orig = [b.clone() for b in bufs]
+        flags = [torch.zeros(64, dtype=torch.int32, device=dev()) for _ in range(world)]
+        epoch = 5
+        for f in flags:
+            f[:16] = epoch
+        bt = (ctypes.c_void_p * world)(*[b.data_ptr() for b in bufs])
+        ft = (ctypes.c_void_p * world)(*[f.data_ptr() for f in flags])
+        for r in range(world):
+            _lib.call("b2_peer_allreduce", bt, ft, world, r, 0, n, _lib.dtype_code(dtype), 1.0 / world, epoch, 1, 0,
+                      torch.cuda.current_stream().cuda_stream)
+        torch.cuda.synchronize()
+        acc = torch.zeros(n, dtype=torch.float32, device=dev())
+        for o in orig:
+            acc += o.float()
+        want = (acc * np.float32(1.0 / world)).to(dtype)
+        for b in bufs:
+            if world == 2 or dtype == torch.float32:
+                assert torch.equal(b, want)               # fixed rank order: bit-exact against the same fp32 sum
+            else:
+                assert (b.float() - want.float()).abs().max() <= float(want.float().abs().max()) * 2 ** -7
+        assert all(torch.equal(b, bufs[0]) for b in bufs)  # every rank holds identical bits
+        total = sum(float(flags[r].view(torch.float32)[32 + r].item()) for r in range(world))
+        np.testing.assert_allclose(total, bufs[0].float().double().pow(2).sum().item(), rtol=1e-5)
+        # reduce-scatter + all-gather halves give the same result
+        bufs2 = [o.clone() for o in orig]
+        bt2 = (ctypes.c_void_p * world)(*[b.data_ptr() for b in bufs2])
+        for r in range(world):
+            _lib.call("b2_peer_allreduce", bt2, ft, world, r, 0, n, _lib.dtype_code(dtype), 1.0 / world, epoch, 0, 1,
+                      torch.cuda.current_stream().cuda_stream)
+        for r in range(world):
+            _lib.call("b2_peer_allgather", bt2, ft, world, r, 0, n, _lib.dtype_code(dtype), epoch,
+                      torch.cuda.current_stream().cuda_stream)
+        torch.cuda.synchronize()
+        for b in bufs2:
+            assert torch.equal(b, bufs[0])

@@ -249,9 +249,10 @@ def test_adamw_bf16_params(ops, state_dtype):
         po, mo, vo = O.adamw_step(p, g, m0, v0, step=1, state_bf16=True, **hp)
         assert (np.abs(mt.float().cpu().numpy() - mo) <= O.bf16_ulp(mo) + 1e-38).all()
         assert (np.abs(vt.float().cpu().numpy() - vo) <= O.bf16_ulp(vo) + 1e-38).all()
-        # 1 bf16 ulp at the magnitude of the operands (an update that crosses zero cancels, so the ulp of the
-        # tiny result is not the right yardstick)
-        assert (np.abs(pt.float().cpu().numpy() - po) <= O.bf16_ulp(np.maximum(np.abs(po), np.abs(p)))).all()
+        # 1 bf16 ulp at the magnitude of the operands (an update that crosses zero cancels, so the ulp of the tiny
+        # result is not the right yardstick) + 2 % of the update size lr*|m^/sqrt(v^)| <= lr: torch's op-by-op bf16
+        # rounding of m, v and the denominator perturbs the update itself by about three half-ulps (2^-9 each)
+        assert (np.abs(pt.float().cpu().numpy() - po) <= O.bf16_ulp(np.maximum(np.abs(po), np.abs(p))) + 0.02 * hp["lr"]).all()
     else:
         np.testing.assert_allclose(mt.cpu().numpy(), me, rtol=1e-6, atol=1e-12)
         np.testing.assert_allclose(vt.cpu().numpy(), ve, rtol=1e-6, atol=1e-16)
