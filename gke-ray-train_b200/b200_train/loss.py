@@ -13,7 +13,7 @@ import torch.nn as nn
 from . import ops
 from ._lib import B2Error
 
-DEFAULT_CHUNK_ROWS = 4096
+DEFAULT_CHUNK_ROWS = 8192
 
 
 def _gscale(grad_out, result, reduction, num_items):

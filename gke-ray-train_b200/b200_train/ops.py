@@ -194,14 +194,21 @@ def lmhead_ce_bwd_dlogits(H, W, labels, lse, gscale, row0, rows, out, bias=None,
     return out
 
 
-def gemm_bf16(A, B, C, M, N, K, a_mn_major=False, b_mn_major=False, accumulate=False):
-    """C[M,N] (+)= A[M,K] @ B[N,K]^T. A is stored [M, lda] (K-major) or [K, lda] (MN-major); same for B."""
+def gemm_bf16(A, B, C, M, N, K, a_mn_major=False, b_mn_major=False, accumulate=False, split_k=True):
+    """C[M,N] (+)= A[M,K] @ B[N,K]^T. A is stored [M, lda] (K-major) or [K, lda] (MN-major); same for B.
+    split_k: hand the kernel fp32 scratch so it may split K when the output alone cannot fill the SMs."""
     require_cuda(A, B, C)
     if A.dtype != torch.bfloat16 or B.dtype != torch.bfloat16:
         raise B2Error("gemm_bf16: A and B must be bfloat16")
     if A.stride(1) != 1 or B.stride(1) != 1 or C.stride(1) != 1:
         raise B2Error("gemm_bf16: unit inner stride required")
     with torch.cuda.device(A.device):
+        ws, ws_bytes = None, 0
+        tiles = ((M + 127) // 128) * ((N + 255) // 256)
+        if split_k and tiles < 3 * 148 and K >= 2048:
+            ws_bytes = _lib.lib.b2_gemm_workspace_bytes(int(M), int(N))
+            ws = torch.empty(ws_bytes, dtype=torch.uint8, device=A.device)
         call("b2_gemm_bf16", ptr(A), int(a_mn_major), A.stride(0), ptr(B), int(b_mn_major), B.stride(0), ptr(C),
-             dtype_code(C.dtype), C.stride(0), int(M), int(N), int(K), int(bool(accumulate)), stream_ptr())
+             dtype_code(C.dtype), C.stride(0), int(M), int(N), int(K), int(bool(accumulate)), ptr(ws), ws_bytes,
+             stream_ptr())
     return C

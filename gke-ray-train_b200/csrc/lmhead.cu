@@ -24,7 +24,9 @@
 #include "b2_common.cuh"
 #include "umma.cuh"
 #include <math.h>
+#include <map>
 #include <mutex>
+#include <tuple>
 
 int b2_ce_finalize_launch(const float* lse, const float* zt, const long long* labels, long long N, long long V,
                           int shift_T, long long ignore_index, float* loss_out, long long* n_valid_out, int* err_out,
@@ -49,6 +51,8 @@ enum { MODE_GEMM = 0, MODE_CE_FWD = 1, MODE_CE_BWD = 2 };
 struct Params {
   int M, N, K;                       // rows (tokens), columns (vocab or features), reduction extent
   int num_m_blocks, num_n_blocks, num_k_blocks, n_splits;
+  int k_splits, n_fastest;           // MODE_GEMM only: split-K factor; unit order (1: units sharing an A tile are adjacent)
+  float* ws; long long ldws;         // split-K partial sums [k_splits][M][ldws] fp32
   // MODE_GEMM
   void* C; long long ldc; int c_dtype; int accumulate;
   // cross-entropy modes
@@ -67,6 +71,24 @@ __device__ __forceinline__ float fast_exp2(float x) {
 __device__ __forceinline__ long long label_at(const Params& p, long long i) {
   if (p.shift_T <= 0) return p.labels[i];
   return ((i % p.shift_T) + 1 < p.shift_T) ? p.labels[i + 1] : p.ignore_index;
+}
+
+struct Unit { int mb, s, ks, nb0, nb1, kb0, kb1; };
+
+// Work unit u -> (128-row block, vocabulary/column range, K range). Units that are adjacent in u run at the same
+// time on neighbouring CTAs, so the fastest-varying coordinate decides which operand tile they share through L2.
+__device__ __forceinline__ Unit decode_unit(const Params& p, int u) {
+  Unit t;
+  const int per_k = p.num_m_blocks * p.n_splits;
+  t.ks = u / per_k;
+  const int r = u - t.ks * per_k;
+  if (p.n_fastest) { t.mb = r / p.n_splits; t.s = r - t.mb * p.n_splits; }
+  else { t.s = r / p.num_m_blocks; t.mb = r - t.s * p.num_m_blocks; }
+  t.nb0 = (int)((long long)t.s * p.num_n_blocks / p.n_splits);
+  t.nb1 = (int)((long long)(t.s + 1) * p.num_n_blocks / p.n_splits);
+  t.kb0 = (int)((long long)t.ks * p.num_k_blocks / p.k_splits);
+  t.kb1 = (int)((long long)(t.ks + 1) * p.num_k_blocks / p.k_splits);
+  return t;
 }
 
 template <int MODE, int A_MN, int B_MN>
@@ -91,18 +113,17 @@ umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
   tc_fence_after();
   const uint32_t tmem_base = tmem_holder;
 
-  const int num_units = p.num_m_blocks * p.n_splits;
+  const int num_units = p.num_m_blocks * p.n_splits * p.k_splits;
 
   if (warp == 0) {
     // ------------------------------------------------------------ TMA producer
     if (lane == 0) {
       int stage = 0; uint32_t phase = 0;
       for (int u = blockIdx.x; u < num_units; u += gridDim.x) {
-        const int mb = u % p.num_m_blocks, s = u / p.num_m_blocks;
-        const int nb0 = (int)((long long)s * p.num_n_blocks / p.n_splits);
-        const int nb1 = (int)((long long)(s + 1) * p.num_n_blocks / p.n_splits);
-        for (int nb = nb0; nb < nb1; ++nb) {
-          for (int kb = 0; kb < p.num_k_blocks; ++kb) {
+        const Unit t = decode_unit(p, u);
+        const int mb = t.mb;
+        for (int nb = t.nb0; nb < t.nb1; ++nb) {
+          for (int kb = t.kb0; kb < t.kb1; ++kb) {
             mbar_wait(&empty_bar[stage], phase ^ 1);
             mbar_arrive_expect_tx(&full_bar[stage], STAGE_BYTES);
             uint8_t* sa = smem + stage * STAGE_BYTES;
@@ -129,14 +150,12 @@ umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
       int stage = 0; uint32_t phase = 0;
       int as = 0; uint32_t aphase = 0;
       for (int u = blockIdx.x; u < num_units; u += gridDim.x) {
-        const int s = u / p.num_m_blocks;
-        const int nb0 = (int)((long long)s * p.num_n_blocks / p.n_splits);
-        const int nb1 = (int)((long long)(s + 1) * p.num_n_blocks / p.n_splits);
-        for (int nb = nb0; nb < nb1; ++nb) {
+        const Unit t = decode_unit(p, u);
+        for (int nb = t.nb0; nb < t.nb1; ++nb) {
           mbar_wait(&tempty_bar[as], aphase ^ 1);
           tc_fence_after();
           const uint32_t tmem_d = tmem_base + (uint32_t)(as * BN);
-          for (int kb = 0; kb < p.num_k_blocks; ++kb) {
+          for (int kb = t.kb0; kb < t.kb1; ++kb) {
             mbar_wait(&full_bar[stage], phase);
             tc_fence_after();
             const uint32_t a_addr = smem_u32(smem + stage * STAGE_BYTES);
@@ -147,7 +166,7 @@ umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
                                           : make_sdesc_sw128(a_addr + k * (UK * 2), 16, 1024);
               const uint64_t bdesc = B_MN ? make_sdesc_sw128(b_addr + k * (UK * 128), BOX_MN_BYTES, 1024)
                                           : make_sdesc_sw128(b_addr + k * (UK * 2), 16, 1024);
-              mma_bf16_ss(tmem_d, adesc, bdesc, idesc, (uint32_t)((kb | k) != 0));
+              mma_bf16_ss(tmem_d, adesc, bdesc, idesc, (uint32_t)(kb > t.kb0 || k > 0));
             }
             mma_commit(&empty_bar[stage]);          // frees the smem slot once these MMAs retire
             if (++stage == STAGES) { stage = 0; phase ^= 1; }
@@ -163,9 +182,8 @@ umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
     const int trow = q * 32 + lane;                 // row inside the tile
     int as = 0; uint32_t aphase = 0;
     for (int u = blockIdx.x; u < num_units; u += gridDim.x) {
-      const int mb = u % p.num_m_blocks, s = u / p.num_m_blocks;
-      const int nb0 = (int)((long long)s * p.num_n_blocks / p.n_splits);
-      const int nb1 = (int)((long long)(s + 1) * p.num_n_blocks / p.n_splits);
+      const Unit t = decode_unit(p, u);
+      const int mb = t.mb, s = t.s, nb0 = t.nb0, nb1 = t.nb1;
       const long long row = (long long)mb * BM + trow;
       const bool row_ok = row < p.M;
 
@@ -195,7 +213,16 @@ umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
           tmem_ld_wait();
 
           if (MODE == MODE_GEMM) {
-            if (row_ok) {
+            if (row_ok && p.k_splits > 1) {
+              // split-K: plain fp32 partial tile; splitk_reduce_kernel adds the splits in a fixed order
+              float* dst = p.ws + ((long long)t.ks * p.M + row) * p.ldws + col0;     // ldws % 4 == 0, col0 % 32 == 0
+              const int ncol = min(32, p.N - col0);
+#pragma unroll
+              for (int j = 0; j < 32; j += 4)
+                if (j < ncol)
+                  *reinterpret_cast<float4*>(dst + j) = make_float4(__uint_as_float(r[j]), __uint_as_float(r[j + 1]),
+                                                                    __uint_as_float(r[j + 2]), __uint_as_float(r[j + 3]));
+            } else if (row_ok) {
               const int ncol = min(32, p.N - col0);
               if (p.c_dtype == B2_F32) {
                 float* dst = static_cast<float*>(p.C) + row * p.ldc + col0;
@@ -331,6 +358,36 @@ __global__ void __launch_bounds__(256) ce_combine_kernel(const float2* __restric
   lse[row] = m + logf(s);
 }
 
+// C[M,N] (+)= sum over splits of ws[k][M][ldws]; 4 columns per thread
+__global__ void __launch_bounds__(256) splitk_reduce_kernel(const float* __restrict__ ws, int k_splits, int M, int N,
+                                                            long long ldws, void* __restrict__ C, int c_dtype,
+                                                            long long ldc, int accumulate) {
+  const long long nq = ldws >> 2;
+  const long long total = (long long)M * nq;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+    const long long row = i / nq;
+    const int col = (int)(i - row * nq) * 4;
+    if (col >= N) continue;
+    float4 acc = *reinterpret_cast<const float4*>(ws + row * ldws + col);
+    for (int k = 1; k < k_splits; ++k) {
+      const float4 v = *reinterpret_cast<const float4*>(ws + ((long long)k * M + row) * ldws + col);
+      acc.x += v.x; acc.y += v.y; acc.z += v.z; acc.w += v.w;
+    }
+    const float a[4] = {acc.x, acc.y, acc.z, acc.w};
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      if (col + j >= N) break;
+      if (c_dtype == B2_F32) {
+        float* d = static_cast<float*>(C) + row * ldc + col + j;
+        *d = a[j] + (accumulate ? *d : 0.f);
+      } else {
+        __nv_bfloat16* d = static_cast<__nv_bfloat16*>(C) + row * ldc + col + j;
+        *d = __float2bfloat16_rn(a[j] + (accumulate ? __bfloat162float(*d) : 0.f));
+      }
+    }
+  }
+}
+
 // ------------------------------------------------------------------ host side
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
                                   const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
@@ -387,7 +444,7 @@ template <int MODE, int A_MN, int B_MN>
 int launch(const CUtensorMap& ta, const CUtensorMap& tb, const Params& p, cudaStream_t stream) {
   auto kern = umma_kernel<MODE, A_MN, B_MN>;
   B2_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
-  const int units = p.num_m_blocks * p.n_splits;
+  const int units = p.num_m_blocks * p.n_splits * p.k_splits;
   const int grid = units < num_sms() ? units : num_sms();
   kern<<<grid, 256, SMEM_BYTES, stream>>>(ta, tb, p);
   B2_CHECK_CUDA(cudaGetLastError());
@@ -405,6 +462,15 @@ int make_operand_tmap(CUtensorMap* m, const void* ptr, int mn_major, long long e
 // Pick how many contiguous vocabulary ranges each 128-row block is split into so that the persistent
 // grid finishes with the least idle time (units are dealt round-robin to CTAs).
 int choose_splits(int num_m_blocks, int num_n_blocks, int grid) {
+  // the search below costs ~1 ms of host time at GPT-2 sizes: remember the answer per shape
+  static std::mutex mu;
+  static std::map<std::tuple<int, int, int>, int> cache;
+  const auto key = std::make_tuple(num_m_blocks, num_n_blocks, grid);
+  {
+    std::lock_guard<std::mutex> lk(mu);
+    auto it = cache.find(key);
+    if (it != cache.end()) return it->second;
+  }
   int best_s = 1; double best = 1e30;
   const int smax = num_n_blocks < MAX_SPLITS ? num_n_blocks : MAX_SPLITS;
   for (int S = 1; S <= smax; ++S) {
@@ -423,13 +489,30 @@ int choose_splits(int num_m_blocks, int num_n_blocks, int grid) {
     }
     if (worst < best - 1e-9) { best = worst; best_s = S; }
   }
+  std::lock_guard<std::mutex> lk(mu);
+  cache[key] = best_s;
   return best_s;
 }
 
 }  // namespace
 
+// split-K factor for a plain GEMM: used when the output has too few 128x256 tiles to fill the 148 SMs
+static int auto_k_splits(int tiles, int num_k_blocks, int sms) {
+  if (tiles >= 3 * sms || num_k_blocks < 32) return 1;
+  int ks = (4 * sms + tiles - 1) / tiles;
+  if (ks > 4) ks = 4;
+  while (ks > 1 && num_k_blocks / ks < 16) --ks;
+  return ks;
+}
+
+extern "C" size_t b2_gemm_workspace_bytes(int M, int N) {
+  const size_t ldws = ((size_t)N + 3) / 4 * 4;
+  return (size_t)4 * (size_t)M * ldws * sizeof(float);
+}
+
 extern "C" int b2_gemm_bf16(const void* A, int a_mn_major, long long lda, const void* B, int b_mn_major, long long ldb,
-                            void* C, int c_dtype, long long ldc, int M, int N, int K, int accumulate, cudaStream_t stream) {
+                            void* C, int c_dtype, long long ldc, int M, int N, int K, int accumulate, void* workspace,
+                            size_t workspace_bytes, cudaStream_t stream) {
   B2_REQUIRE(M >= 1 && N >= 1 && K >= 1, "b2_gemm_bf16: bad shape M=%d N=%d K=%d", M, N, K);
   B2_REQUIRE(A && B && C, "b2_gemm_bf16: null pointer");
   B2_REQUIRE(c_dtype == B2_F32 || c_dtype == B2_BF16, "b2_gemm_bf16: c_dtype must be 0 (f32) or 1 (bf16)");
@@ -442,11 +525,23 @@ extern "C" int b2_gemm_bf16(const void* A, int a_mn_major, long long lda, const 
   p.M = M; p.N = N; p.K = K;
   p.num_m_blocks = (M + BM - 1) / BM; p.num_n_blocks = (N + BN - 1) / BN; p.num_k_blocks = (K + BK - 1) / BK;
   p.n_splits = p.num_n_blocks;
+  p.n_fastest = p.num_n_blocks <= 8;     // few column blocks: let the CTAs that share an A row-block run side by side
+  p.k_splits = 1;
+  if (workspace != nullptr && workspace_bytes >= b2_gemm_workspace_bytes(M, N) && b2_aligned(workspace, 16))
+    p.k_splits = auto_k_splits(p.num_m_blocks * p.num_n_blocks, p.num_k_blocks, num_sms());
+  p.ws = static_cast<float*>(workspace); p.ldws = ((long long)N + 3) / 4 * 4;
   p.C = C; p.ldc = ldc; p.c_dtype = c_dtype; p.accumulate = accumulate;
-  if (!a_mn_major && !b_mn_major) return launch<MODE_GEMM, 0, 0>(ta, tb, p, stream);
-  if (!a_mn_major && b_mn_major) return launch<MODE_GEMM, 0, 1>(ta, tb, p, stream);
-  if (a_mn_major && !b_mn_major) return launch<MODE_GEMM, 1, 0>(ta, tb, p, stream);
-  return launch<MODE_GEMM, 1, 1>(ta, tb, p, stream);
+  if (!a_mn_major && !b_mn_major) rc = launch<MODE_GEMM, 0, 0>(ta, tb, p, stream);
+  else if (!a_mn_major && b_mn_major) rc = launch<MODE_GEMM, 0, 1>(ta, tb, p, stream);
+  else if (a_mn_major && !b_mn_major) rc = launch<MODE_GEMM, 1, 0>(ta, tb, p, stream);
+  else rc = launch<MODE_GEMM, 1, 1>(ta, tb, p, stream);
+  if (rc != B2_OK || p.k_splits == 1) return rc;
+  const long long total = (long long)M * (p.ldws / 4);
+  long long blocks = (total + 255) / 256;
+  if (blocks > (long long)num_sms() * 8) blocks = (long long)num_sms() * 8;
+  splitk_reduce_kernel<<<(unsigned)blocks, 256, 0, stream>>>(p.ws, p.k_splits, M, N, p.ldws, C, c_dtype, ldc, accumulate);
+  B2_CHECK_CUDA(cudaGetLastError());
+  return B2_OK;
 }
 
 extern "C" size_t b2_lmhead_ce_workspace_bytes(long long N) {
@@ -475,6 +570,7 @@ extern "C" int b2_lmhead_ce_fwd(const void* H, long long ldh, const void* W, lon
     p.M = (int)N; p.N = V; p.K = D;
     p.num_m_blocks = (int)((N + BM - 1) / BM); p.num_n_blocks = (V + BN - 1) / BN; p.num_k_blocks = (D + BK - 1) / BK;
     p.n_splits = choose_splits(p.num_m_blocks, p.num_n_blocks, num_sms());
+    p.k_splits = 1; p.n_fastest = 0;
     p.labels = labels; p.shift_T = shift_T; p.ignore_index = ignore_index; p.row0 = 0;
     p.bias = bias; p.round_bf16 = round_logits_bf16;
     p.part = static_cast<float2*>(workspace); p.part_stride = (long long)p.num_m_blocks * BM; p.zt = zt;
@@ -502,7 +598,7 @@ extern "C" int b2_lmhead_ce_bwd_dlogits(const void* H, long long ldh, const void
   Params p{};
   p.M = (int)rows; p.N = V; p.K = D;
   p.num_m_blocks = (int)((rows + BM - 1) / BM); p.num_n_blocks = (V + BN - 1) / BN; p.num_k_blocks = (D + BK - 1) / BK;
-  p.n_splits = p.num_n_blocks;
+  p.n_splits = p.num_n_blocks; p.k_splits = 1; p.n_fastest = 0;
   p.labels = labels; p.shift_T = shift_T; p.ignore_index = ignore_index; p.row0 = row0;
   p.bias = bias; p.round_bf16 = round_logits_bf16;
   p.lse = lse; p.gscale = gscale_dev; p.dlogits = static_cast<__nv_bfloat16*>(dlogits); p.ldd = ldd;

@@ -126,7 +126,12 @@ int b2_lmhead_ce_bwd_dlogits(const void* H, long long ldh, const void* W, long l
  * Used for dH = dlogits * W and dW += dlogits^T * H, replacing the autograd GEMMs of nn.Linear
  * (ref: the loss.backward() at ray-jobs/pytorch_llm_ray.py:276). */
 int b2_gemm_bf16(const void* A, int a_mn_major, long long lda, const void* B, int b_mn_major, long long ldb, void* C,
-                 int c_dtype, long long ldc, int M, int N, int K, int accumulate, b2_stream_t stream);
+                 int c_dtype, long long ldc, int M, int N, int K, int accumulate, void* workspace,
+                 size_t workspace_bytes, b2_stream_t stream);
+/* Optional split-K scratch for b2_gemm_bf16: when `workspace` holds at least b2_gemm_workspace_bytes(M, N) bytes and
+ * the output has too few 128x256 tiles to occupy the 148 SMs (e.g. dH: M = tokens, N = D, K = vocabulary), the K
+ * range is split up to 4 ways into fp32 partials that a second kernel adds in a fixed order. NULL = never split. */
+size_t b2_gemm_workspace_bytes(int M, int N);
 
 /* ---- F2: gradient all-reduce over peer memory (NVLink 5 / NVSwitch) ----------------------------------
  * Replaces the bucket all-reduce (+ the grad / world_size copy-in) that DistributedDataParallel performs during

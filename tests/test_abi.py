@@ -44,6 +44,7 @@ def test_version_and_sizes(lib):
     assert lib.lib.b2_peer_flags_bytes() == 256
     assert lib.lib.b2_lmhead_ce_workspace_bytes(8192) == 64 * 8192 * 8
     assert lib.lib.b2_lmhead_ce_workspace_bytes(1) == 64 * 128 * 8
+    assert lib.lib.b2_gemm_workspace_bytes(100, 770) == 4 * 100 * 772 * 4
 
 
 def test_bad_arguments_are_rejected_without_a_gpu(lib):

@@ -271,3 +271,22 @@ def test_adamw_clip_coef_is_applied(ops):
     pe, me, ve = O.adamw_step(p, clipped[0], np.zeros(n, np.float32), np.zeros(n, np.float32), step=1, **hp)
     np.testing.assert_allclose(mt.cpu().numpy(), me, rtol=2e-6)
     np.testing.assert_allclose(pt.cpu().numpy(), pe, rtol=1e-6, atol=1e-7)
+
+
+def test_gemm_split_k_matches_unsplit(ops):
+    """dH-shaped GEMM (few output tiles, long K): the split-K path must agree with the single-pass path."""
+    rng = np.random.default_rng(21)
+    M, N, K = 512, 768, 50257
+    ldk = (K + 7) // 8 * 8
+    A = torch.zeros(M, ldk, dtype=torch.bfloat16, device=dev()); A[:, :K] = torch.from_numpy(O.bf16_round(rng.standard_normal((M, K)).astype(np.float32) * 0.01)).to(dev())
+    B = torch.from_numpy(O.bf16_round(rng.standard_normal((K, N)).astype(np.float32))).to(dev()).to(torch.bfloat16)   # MN-major B
+    C1 = torch.empty(M, N, dtype=torch.bfloat16, device=dev()); C2 = torch.empty_like(C1)
+    ops.gemm_bf16(A, B, C1, M, N, K, b_mn_major=True, split_k=False)
+    ops.gemm_bf16(A, B, C2, M, N, K, b_mn_major=True, split_k=True)
+    ref = A[:, :K].float() @ B.float()
+    for C in (C1, C2):
+        assert ((C.float() - ref).abs() <= 2.0 ** -7 * ref.abs() + 2e-3).all()
+    # accumulate through the split path
+    C3 = torch.ones(M, N, dtype=torch.float32, device=dev())
+    ops.gemm_bf16(A, B, C3, M, N, K, b_mn_major=True, accumulate=True)
+    assert ((C3 - 1 - ref).abs() <= 1e-3 * ref.abs().max()).all()

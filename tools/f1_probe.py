@@ -32,7 +32,7 @@ def main():
     ap.add_argument("--D", type=int, default=768)
     ap.add_argument("--V", type=int, default=50257)
     ap.add_argument("--T", type=int, default=1024)
-    ap.add_argument("--chunk", type=int, default=4096)
+    ap.add_argument("--chunk", type=int, default=8192)
     ap.add_argument("--adamw", action="store_true")
     args = ap.parse_args()
     from b200_train import ops
