@@ -186,11 +186,21 @@ def run_ours(args):
     peaks = load_peaks()
     model = TR.make_gpt2(dtype=torch.bfloat16, seed=0)
     model.train()
-    b200.patch_causal_lm(model)
-    model = b200.prepare_model(model)                       # .to(device); peer-memory DDP when world > 1
-    inner = model.module if hasattr(model, "module") else model
+    stock = args.impl == "stock-gpu"       # informational third arm: the reference's stock torch path on THIS GPU
+    if stock:
+        model = model.to(device)
+        if world > 1:
+            model = torch.nn.parallel.DistributedDataParallel(model, device_ids=[local_rank])
+        inner = model.module if hasattr(model, "module") else model
+        optimizer = torch.optim.AdamW(TR.hf_param_groups(inner, WD), lr=LR)
+        clip = torch.nn.utils.clip_grad_norm_
+    else:
+        b200.patch_causal_lm(model)
+        model = b200.prepare_model(model)                   # .to(device); peer-memory DDP when world > 1
+        inner = model.module if hasattr(model, "module") else model
+        optimizer = b200.AdamW(TR.hf_param_groups(inner, WD), lr=LR)
+        clip = b200.clip_grad_norm_
     V = inner.config.vocab_size
-    optimizer = b200.AdamW(TR.hf_param_groups(inner, WD), lr=LR)
 
     n_batches = 4
     host = [TR.synthetic_hf_batch(B_PER_GPU, SEQ, V, 1234 + 97 * rank + i) for i in range(n_batches)]
@@ -201,7 +211,7 @@ def run_ours(args):
         optimizer.zero_grad(set_to_none=True)
         loss = model(input_ids=ids, labels=labels).loss
         loss.backward()
-        b200.clip_grad_norm_(model.parameters(), MAX_NORM)
+        clip(model.parameters(), MAX_NORM)
         optimizer.step()
         return loss
 
@@ -246,17 +256,18 @@ def run_ours(args):
     e2e = tokens_per_step * args.steps / (ms_e2e * 1e-3)
 
     roof = cpu = extra = None
-    if rank == 0:
+    if rank == 0 and not stock:
         roof = f1_roofline(torch, b200, inner, device, peaks)
         extra = [f3_roofline(torch, ops, device, peaks)]
     if world > 1:
         dist.barrier()
-    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+    if rank == 0 and world == 1 and not args.no_cpu_baseline and not stock:
         torch.set_num_threads(os.cpu_count() or 1)
         r = TR.cpu_gpt2_baseline(steps=2, warmup=1, B=1, T=SEQ, dtype=torch.bfloat16)
         cpu = {"value": r["tokens_per_s"], "unit": "tokens/s", "cores": r["threads"], "kind": "port", "sample": r["sample"]}
     if rank == 0:
         line = {
+            **({"impl": "stock-gpu"} if stock else {}),
             "metric": METRIC, "value": value, "unit": "tokens/s", "n_gpus": world, "steps": args.steps,
             "warmup": max(args.warmup, 3), "ms_per_step": ms_total / args.steps, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
@@ -283,7 +294,7 @@ def main():
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
-    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference", "stock-gpu"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
     if args.impl == "reference":
@@ -293,7 +304,7 @@ def main():
         # convenience: re-launch ourselves one rank per GPU
         cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={args.gpus}",
                "--master-addr", "127.0.0.1", "--master-port", "29517", os.path.abspath(__file__), "--gpus", str(args.gpus),
-               "--steps", str(args.steps), "--warmup", str(args.warmup)] + (["--no-cpu-baseline"] if args.no_cpu_baseline else [])
+               "--steps", str(args.steps), "--warmup", str(args.warmup), "--impl", args.impl] + (["--no-cpu-baseline"] if args.no_cpu_baseline else [])
         raise SystemExit(subprocess.call(cmd))
     run_ours(args)
 
