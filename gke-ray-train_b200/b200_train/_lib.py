@@ -40,6 +40,8 @@ _SIGS = {
                                  c_void_p, c_int, c_void_p, c_void_p]),
     "b2_sumsq_scratch_bytes": (c_size_t, []),
     "b2_sumsq": (c_int, [c_void_p, c_size_t, c_int, c_void_p, c_void_p, c_int, c_void_p]),
+    "b2_sumsq_static_max_elems": (c_size_t, []),
+    "b2_sumsq_static": (c_int, [c_void_p, c_size_t, c_int, c_void_p, c_int, c_void_p]),
     "b2_clip_coef": (c_int, [c_void_p, c_int, c_float, c_void_p, c_void_p, c_void_p]),
     "b2_scale": (c_int, [c_void_p, c_size_t, c_int, c_void_p, c_void_p]),
     "b2_ce_rows_fwd": (c_int, [c_void_p, c_int, c_longlong, c_longlong, c_longlong, c_void_p, c_int, c_longlong,
@@ -76,7 +78,7 @@ EXPORTS = tuple(_SIGS)
 
 # number of kernels this process has enqueued through the library (bench.py reports it)
 launch_count = 0
-_LAUNCHES = {"b2_adamw": 1, "b2_adamw_grouped": 1, "b2_sumsq": 1, "b2_clip_coef": 1, "b2_scale": 1, "b2_ce_rows_fwd": 2,
+_LAUNCHES = {"b2_adamw": 1, "b2_adamw_grouped": 1, "b2_sumsq": 1, "b2_sumsq_static": 1, "b2_clip_coef": 1, "b2_scale": 1, "b2_ce_rows_fwd": 2,
              "b2_ce_rows_bwd": 1, "b2_lmhead_ce_fwd": 3, "b2_lmhead_ce_bwd_dlogits": 1, "b2_gemm_bf16": 1,  # (+1 reduce launch when split-K kicks in)
              "b2_peer_allreduce": 1, "b2_peer_allgather": 1}
 

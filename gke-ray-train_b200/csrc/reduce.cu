@@ -9,6 +9,7 @@
 //
 // HBM-bound: algorithmic bytes = n * sizeof(dtype) read (sumsq), + the same written (scale).
 #include "b2_common.cuh"
+#include <mutex>
 
 // scratch layout for b2_sumsq: word 0 = arrival ticket (self-resetting), words [32, 32+blocks) = per-block partials
 #define B2_SUMSQ_MAX_BLOCKS (B2_NUM_SMS * 8)
@@ -145,6 +146,85 @@ extern "C" int b2_scale(void* g, size_t n, int dtype, const float* coef_dev, cud
   const unsigned grid = grid_for(n, (size_t)B2_NUM_SMS * 16);
   if (dtype == B2_F32) scale_kernel<B2_F32><<<grid, 256, 0, stream>>>(g, n, coef_dev);
   else scale_kernel<B2_BF16><<<grid, 256, 0, stream>>>(g, n, coef_dev);
+  B2_CHECK_CUDA(cudaGetLastError());
+  return B2_OK;
+}
+
+// ---------------------------------------------------------------------------------------------------------------------
+// b2_sumsq_static — the same sum of squares for callers that have no way to hand us scratch memory.
+//
+// Who that is: a host that only holds the pointers it was given (a C, Go or JVM binding with no device allocator of
+// its own); a process whose framework allocator has already claimed the whole GPU, so a raw cudaMalloc from a side
+// library fails or fragments the pool; and code running where an allocation's implicit device-wide synchronisation
+// is not acceptable, such as a gradient hook called from the autograd engine's thread in the middle of backward.
+// For them the per-block partials and the arrival ticket live in the fixed array below, which is part of the library
+// image: every GPU that loads libb2train.so carries these few KB until the process exits.
+//
+// Limits and rules:
+//   * at most B2_SUMSQ_STATIC_MAX_N elements per call (larger inputs are rejected with B2_ERR_LIMIT — split the buffer
+//     and use accumulate=1 for the later pieces);
+//   * the first call on each device looks the array's device address up (cudaGetSymbolAddress, that device current)
+//     and remembers it; make that first call before starting any stream capture;
+//   * all calls on a device share the one array, which still holds whatever the previous call left there. The only
+//     word that has to start at zero, the arrival ticket, is cleared at the start of every call; the partials are
+//     overwritten before they are read;
+//   * because the array is shared, two calls that may run on the GPU at the same time (different streams, or different
+//     host threads on one device) race on it. Issue them on one stream, or order them with events.
+// Nothing here calls cudaMalloc, cudaFree or any routine that allocates.
+#define B2_SUMSQ_STATIC_BLOCKS (B2_NUM_SMS * 4)
+#define B2_SUMSQ_STATIC_WORDS (32 + B2_SUMSQ_STATIC_BLOCKS)      /* 624 floats = 2496 bytes */
+#define B2_SUMSQ_STATIC_MAX_N ((size_t)1 << 31)
+#define B2_MAX_DEVICES 64
+
+static __device__ __align__(256) float g_sumsq_static_scratch[B2_SUMSQ_STATIC_WORDS];
+
+// In host code the name g_sumsq_static_scratch is only a handle for the symbol, not an address the GPU can use;
+// the real device address has to be asked for, once per device.
+static float* sumsq_static_scratch_ptr(int* rc_out) {
+  static float* ptrs[B2_MAX_DEVICES] = {nullptr};
+  static std::mutex mu;
+  *rc_out = B2_OK;
+  int dev = -1;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess || dev < 0 || dev >= B2_MAX_DEVICES) {
+    b2_set_error("b2_sumsq_static: cannot identify the current device (%s)", e == cudaSuccess ? "index out of range" : cudaGetErrorString(e));
+    *rc_out = B2_ERR_CUDA;
+    return nullptr;
+  }
+  std::lock_guard<std::mutex> lk(mu);
+  if (ptrs[dev] == nullptr) {
+    float* p = nullptr;
+    e = cudaGetSymbolAddress((void**)&p, g_sumsq_static_scratch);
+    if (e != cudaSuccess || p == nullptr) {
+      b2_set_error("b2_sumsq_static: cudaGetSymbolAddress failed on device %d: %s", dev, cudaGetErrorString(e));
+      *rc_out = B2_ERR_CUDA;
+      return nullptr;
+    }
+    ptrs[dev] = p;
+  }
+  return ptrs[dev];
+}
+
+extern "C" size_t b2_sumsq_static_max_elems(void) { return B2_SUMSQ_STATIC_MAX_N; }
+
+extern "C" int b2_sumsq_static(const void* g, size_t n, int dtype, float* out, int accumulate, cudaStream_t stream) {
+  B2_REQUIRE(out, "b2_sumsq_static: null out");
+  B2_REQUIRE(n == 0 || g, "b2_sumsq_static: null input");
+  B2_REQUIRE(dtype == B2_F32 || dtype == B2_BF16, "b2_sumsq_static: dtype must be 0 (f32) or 1 (bf16)");
+  B2_REQUIRE(b2_aligned(g, 16), "b2_sumsq_static: input must be 16-byte aligned");
+  if (n > B2_SUMSQ_STATIC_MAX_N) {
+    b2_set_error("b2_sumsq_static: %zu elements exceed the limit of %zu per call; split the buffer and pass accumulate=1 "
+                 "for the later pieces, or use b2_sumsq with caller-provided scratch", n, (size_t)B2_SUMSQ_STATIC_MAX_N);
+    return B2_ERR_LIMIT;
+  }
+  int rc;
+  float* scratch = sumsq_static_scratch_ptr(&rc);
+  if (rc != B2_OK) return rc;
+  // the ticket must read zero when the first block arrives, whatever an earlier (possibly failed) launch left behind
+  B2_CHECK_CUDA(cudaMemsetAsync(scratch, 0, sizeof(unsigned), stream));
+  const unsigned grid = grid_for(n, B2_SUMSQ_STATIC_BLOCKS);
+  if (dtype == B2_F32) sumsq_kernel<B2_F32><<<grid, 256, 0, stream>>>(g, n, scratch, out, accumulate);
+  else sumsq_kernel<B2_BF16><<<grid, 256, 0, stream>>>(g, n, scratch, out, accumulate);
   B2_CHECK_CUDA(cudaGetLastError());
   return B2_OK;
 }

@@ -75,6 +75,19 @@ int b2_clip_coef(const float* sumsq_parts, int nparts, float max_norm, float* no
                  b2_stream_t stream);
 int b2_scale(void* g, size_t n, int dtype, const float* coef_dev, b2_stream_t stream);
 
+/* b2_sumsq for callers that cannot supply scratch memory. It has no counterpart in the reference (the reference never
+ * manages device memory itself); it exists for hosts that only hold the pointers they were handed, for processes whose
+ * framework allocator already owns the whole GPU, and for call sites — a gradient hook on the autograd thread, say —
+ * where an allocation's implicit device synchronisation is unwelcome. The partial sums live in a fixed 2.5 KB array
+ * inside the library image (one copy per GPU that loads the library, held until exit); the call allocates nothing.
+ *   - n <= b2_sumsq_static_max_elems() (2^31) per call, else B2_ERR_LIMIT; split larger buffers and accumulate;
+ *   - the first call on a device resolves the array's address (cudaGetSymbolAddress): do it before any stream capture;
+ *   - every call on a device shares the array (it keeps the previous call's contents; the one word that must be zero
+ *     is cleared per call), so calls that can overlap on the GPU race — keep them on one stream or order them.
+ * out / accumulate as for b2_sumsq. */
+size_t b2_sumsq_static_max_elems(void);
+int b2_sumsq_static(const void* g, size_t n, int dtype, float* out, int accumulate, b2_stream_t stream);
+
 /* ---- cross-entropy over materialised logits -------------------------------------------------------
  * Replace nn.CrossEntropyLoss()(outputs.reshape(-1,V), targets.reshape(-1)) — ref:
  * ray-jobs/pytorch_llm_ray.py:237,275 (labels pre-shifted by TextDataset, ref :116-119).
