@@ -47,7 +47,7 @@ def main():
             if dtype == torch.float32 and world > 2:
                 tol = 1e-6                                    # different fp32 summation order than NCCL's ring
             assert (t.float() - want.float()).abs().max() <= tol, (dtype, it, (t.float() - want.float()).abs().max())
-            bits = t.view(torch.int16 if dtype == torch.bfloat16 else torch.int32).clone()
+            bits = t.view(torch.uint8).clone()
             b0 = bits.clone()
             dist.broadcast(b0, 0)
             assert torch.equal(bits, b0), "ranks hold different bits after the peer all-reduce"
