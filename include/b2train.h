@@ -126,7 +126,8 @@ int b2_lmhead_ce_fwd(const void* H, long long ldh, const void* W, long long ldw,
                      int round_logits_bf16, void* workspace, size_t workspace_bytes, float* lse, float* zt,
                      float* loss_out, long long* n_valid_out, int* err_out, b2_stream_t stream);
 /* Backward, step 1: recomputes the logits of rows [row0, row0+rows) and writes
- *   dlogits[r, j] = (exp(logit - lse[row0+r]) - [j == label]) * gscale_dev[0]   (bf16, [rows, ldd], ldd % 8 == 0)
+ *   dlogits[r, j] = (exp(logit - lse[row0+r]) - [j == label]) * gscale_dev[0]   (bf16, [rows, ldd], ldd % 8 == 0;
+ *   columns [V, ldd) are padding and are not written)
  * H points at row row0 of the hidden states; labels and lse are the full arrays (indexed by row0 + r).
  * dH and dW then follow from two b2_gemm_bf16 calls on this chunk. */
 int b2_lmhead_ce_bwd_dlogits(const void* H, long long ldh, const void* W, long long ldw, const float* bias,
@@ -143,7 +144,7 @@ int b2_gemm_bf16(const void* A, int a_mn_major, long long lda, const void* B, in
                  size_t workspace_bytes, b2_stream_t stream);
 /* Optional split-K scratch for b2_gemm_bf16: when `workspace` holds at least b2_gemm_workspace_bytes(M, N) bytes and
  * the output has too few 128x256 tiles to occupy the 148 SMs (e.g. dH: M = tokens, N = D, K = vocabulary), the K
- * range is split up to 4 ways into fp32 partials that a second kernel adds in a fixed order. NULL = never split. */
+ * range is split up to 6 ways into fp32 partials that a second kernel adds in a fixed order. NULL = never split. */
 size_t b2_gemm_workspace_bytes(int M, int N);
 
 /* ---- F2: gradient all-reduce over peer memory (NVLink 5 / NVSwitch) ----------------------------------

@@ -42,9 +42,9 @@ def test_version_and_sizes(lib):
     assert lib.lib.b2_version() == 100
     assert lib.lib.b2_sumsq_scratch_bytes() >= 4 * (32 + 148)
     assert lib.lib.b2_peer_flags_bytes() == 256
-    assert lib.lib.b2_lmhead_ce_workspace_bytes(8192) == 64 * 8192 * 8
-    assert lib.lib.b2_lmhead_ce_workspace_bytes(1) == 64 * 128 * 8
-    assert lib.lib.b2_gemm_workspace_bytes(100, 770) == 4 * 100 * 772 * 4
+    assert lib.lib.b2_lmhead_ce_workspace_bytes(8192) == 2 * 64 * 8192 * 8
+    assert lib.lib.b2_lmhead_ce_workspace_bytes(1) == 2 * 64 * 128 * 8
+    assert lib.lib.b2_gemm_workspace_bytes(100, 770) == 6 * 100 * 772 * 4
 
 
 def test_bad_arguments_are_rejected_without_a_gpu(lib):

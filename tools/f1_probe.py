@@ -34,6 +34,7 @@ def main():
     ap.add_argument("--T", type=int, default=1024)
     ap.add_argument("--chunk", type=int, default=8192)
     ap.add_argument("--adamw", action="store_true")
+    ap.add_argument("--plain", action="store_true")
     args = ap.parse_args()
     from b200_train import ops
     dev = torch.device("cuda", 0)
@@ -60,6 +61,15 @@ def main():
         n = N if k == "fwd" else chunk
         ms = sorted(ts)[len(ts) // 2]
         print(f"{k:22s} median {ms:8.3f} ms   {2.0 * n * V * D / ms / 1e9:8.1f} TFLOP/s   all={['%.3f' % t for t in ts]}")
+    if args.plain:
+        # fwd-shaped plain GEMM: logits[N, V] = H @ W^T (bf16 out) -- mainloop + the simplest epilogue
+        C = torch.empty(N, ldd, dtype=torch.bfloat16, device=dev)
+        ts = timeit(lambda: ops.gemm_bf16(H, W, C, N, V, D), args.iters, flush)
+        ms = sorted(ts)[len(ts) // 2]
+        print(f"plain gemm [N,V]=H@W^T  median {ms:8.3f} ms   {2.0 * N * V * D / ms / 1e9:8.1f} TFLOP/s   (B2_DEBUG_NOEPI={os.environ.get('B2_DEBUG_NOEPI')})")
+        ts = timeit(lambda: torch.matmul(H, W.t(), out=C[:, :V]) if False else torch.matmul(H, W.t()), args.iters, flush)
+        ms = sorted(ts)[len(ts) // 2]
+        print(f"cuBLAS  H@W^T           median {ms:8.3f} ms   {2.0 * N * V * D / ms / 1e9:8.1f} TFLOP/s")
     if args.adamw:
         n = 1 << 27
         p = torch.randn(n, device=dev).to(torch.bfloat16); gr = (torch.randn(n, device=dev) * 0.01).to(torch.bfloat16)
