@@ -39,14 +39,15 @@ using namespace umma;
 
 constexpr int BM = 128, BN = 256, BK = 64, UK = 16;
 constexpr int NUM_THREADS = 384;                    // warps: 0 TMA, 1 MMA, 2 TMEM alloc, 3 idle, 4-11 epilogue
-constexpr int MAX_STAGES = 4;
-constexpr int A_STAGE_BYTES = BM * BK * 2;            // 16 KiB
-constexpr int B_STAGE_BYTES = BN * BK * 2;            // 32 KiB
-constexpr int STAGE_BYTES = A_STAGE_BYTES + B_STAGE_BYTES;
+constexpr int MAX_STAGES = 6;
+constexpr int A_STAGE_BYTES = BM * BK * 2;            // 16 KiB: this CTA's 128 rows of A
+// B per CTA: all 256 columns (32 KiB) when a CTA works alone, its half of them (16 KiB) in a CTA pair
+constexpr int b_stage_bytes(bool pair) { return (pair ? BN / 2 : BN) * BK * 2; }
+constexpr int stage_bytes(bool pair) { return A_STAGE_BYTES + b_stage_bytes(pair); }
+constexpr int stages_for(bool pair) { return pair ? 6 : 4; }                 // 192 KiB of operand ring either way
 constexpr int STAGING_BYTES = 4 * BM * 64;           // MODE_CE_BWD: 2 column halves x 2 alternating [128 rows x 64 B] boxes
-constexpr int stages_for(int mode) { return 4; }
-constexpr int smem_bytes_for(int mode) {             // + 1 KiB slack to reach 1024-byte alignment
-  return stages_for(mode) * STAGE_BYTES + 1024 + (mode == 2 ? STAGING_BYTES : 0);
+constexpr int smem_bytes_for(int mode, bool pair) {  // + 1 KiB slack to reach 1024-byte alignment
+  return stages_for(pair) * stage_bytes(pair) + 1024 + (mode == 2 ? STAGING_BYTES : 0);
 }
 constexpr int BOX_MN_BYTES = 64 * BK * 2;             // one MN-major TMA box: 64 K-rows x 128 B
 constexpr uint32_t TMEM_COLS = 512;
@@ -99,11 +100,16 @@ __device__ __forceinline__ Unit decode_unit(const Params& p, int u) {
   return t;
 }
 
-template <int MODE, int A_MN, int B_MN>
+// PAIR = true: two CTAs of a cluster share every tile (tcgen05 cta_group::2, M = 256): each loads its own 128 rows of A
+// and half of B, halving the shared-memory traffic per MMA; p.num_m_blocks then counts 256-row blocks.
+template <int MODE, int A_MN, int B_MN, bool PAIR>
 __global__ void __launch_bounds__(NUM_THREADS, 1)
 umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
             const __grid_constant__ CUtensorMap tmD, const Params p) {
-  constexpr int STAGES = stages_for(MODE);
+  constexpr int STAGES = stages_for(PAIR);
+  constexpr int NC = PAIR ? 2 : 1;
+  constexpr int STAGE_BYTES = stage_bytes(PAIR);
+  constexpr int BN_CTA = BN / NC;                   // columns of B this CTA keeps in shared memory
   extern __shared__ uint8_t smem_raw[];
   __shared__ uint64_t full_bar[MAX_STAGES], empty_bar[MAX_STAGES], tfull_bar[2], tempty_bar[2];
   __shared__ uint32_t tmem_holder;
@@ -112,14 +118,19 @@ umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
 
   if (threadIdx.x == 0) { tma_prefetch_desc(&tmA); tma_prefetch_desc(&tmB); if (MODE == MODE_CE_BWD) tma_prefetch_desc(&tmD); }
+  const int crank = PAIR ? (int)cluster_ctarank() : 0;      // 0 = leader of the pair (issues the MMAs)
+  const int cid = (int)blockIdx.x / NC, ncl = (int)gridDim.x / NC;   // this CTA('s pair) and the number of them
   if (threadIdx.x == 32) {
+    // full: the leader's arrive.expect_tx (both CTAs' TMA bytes are credited to the leader's barrier)
+    // empty / tfull: one tcgen05.commit each (multicast to both CTAs in a pair)
+    // tempty: one arrival per epilogue warp of every CTA sharing the accumulator
     for (int i = 0; i < STAGES; ++i) { mbar_init(&full_bar[i], 1); mbar_init(&empty_bar[i], 1); }
-    for (int i = 0; i < 2; ++i) { mbar_init(&tfull_bar[i], 1); mbar_init(&tempty_bar[i], 256); }
+    for (int i = 0; i < 2; ++i) { mbar_init(&tfull_bar[i], 1); mbar_init(&tempty_bar[i], 8 * NC); }
     fence_mbar_init();
   }
-  if (warp == 2) tmem_alloc<TMEM_COLS>(&tmem_holder);
+  if (warp == 2) { if (PAIR) tmem_alloc_pair<TMEM_COLS>(&tmem_holder); else tmem_alloc<TMEM_COLS>(&tmem_holder); }
   tc_fence_before();
-  __syncthreads();
+  if (PAIR) cluster_sync_all(); else __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = tmem_holder;
 
@@ -129,24 +140,28 @@ umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
     // ------------------------------------------------------------ TMA producer
     if (lane == 0) {
       int stage = 0; uint32_t phase = 0;
-      for (int u = blockIdx.x; u < num_units; u += gridDim.x) {
+      for (int u = cid; u < num_units; u += ncl) {
         const Unit t = decode_unit(p, u);
-        const int mb = t.mb;
+        const int m0 = (t.mb * NC + crank) * BM;      // first row of A this CTA loads
         for (int nb = t.nb0; nb < t.nb1; ++nb) {
+          const int n0 = nb * BN + crank * BN_CTA;    // first column of B this CTA loads
           for (int kb = t.kb0; kb < t.kb1; ++kb) {
             mbar_wait(&empty_bar[stage], phase ^ 1);
-            mbar_arrive_expect_tx(&full_bar[stage], STAGE_BYTES);
+            if (crank == 0) mbar_arrive_expect_tx(&full_bar[stage], NC * STAGE_BYTES);
             uint8_t* sa = smem + stage * STAGE_BYTES;
             uint8_t* sb = sa + A_STAGE_BYTES;
-            if (!A_MN) tma_load_2d(sa, &tmA, &full_bar[stage], kb * BK, mb * BM);
+            auto load = [&](void* dst, const CUtensorMap* m, int c0, int c1) {
+              if (PAIR) tma_load_2d_pair(dst, m, &full_bar[stage], c0, c1); else tma_load_2d(dst, m, &full_bar[stage], c0, c1);
+            };
+            if (!A_MN) load(sa, &tmA, kb * BK, m0);
             else {
 #pragma unroll
-              for (int j = 0; j < BM / 64; ++j) tma_load_2d(sa + j * BOX_MN_BYTES, &tmA, &full_bar[stage], mb * BM + j * 64, kb * BK);
+              for (int j = 0; j < BM / 64; ++j) load(sa + j * BOX_MN_BYTES, &tmA, m0 + j * 64, kb * BK);
             }
-            if (!B_MN) tma_load_2d(sb, &tmB, &full_bar[stage], kb * BK, nb * BN);
+            if (!B_MN) load(sb, &tmB, kb * BK, n0);
             else {
 #pragma unroll
-              for (int j = 0; j < BN / 64; ++j) tma_load_2d(sb + j * BOX_MN_BYTES, &tmB, &full_bar[stage], nb * BN + j * 64, kb * BK);
+              for (int j = 0; j < BN_CTA / 64; ++j) load(sb + j * BOX_MN_BYTES, &tmB, n0 + j * 64, kb * BK);
             }
             if (++stage == STAGES) { stage = 0; phase ^= 1; }
           }
@@ -155,11 +170,11 @@ umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
     }
   } else if (warp == 1) {
     // ------------------------------------------------------------ MMA issuer (one thread)
-    if (lane == 0) {
-      constexpr uint32_t idesc = make_idesc_bf16(BM, BN, A_MN, B_MN);
+    if (lane == 0 && crank == 0) {
+      constexpr uint32_t idesc = make_idesc_bf16(BM * NC, BN, A_MN, B_MN);
       int stage = 0; uint32_t phase = 0;
       int as = 0; uint32_t aphase = 0;
-      for (int u = blockIdx.x; u < num_units; u += gridDim.x) {
+      for (int u = cid; u < num_units; u += ncl) {
         const Unit t = decode_unit(p, u);
         for (int nb = t.nb0; nb < t.nb1; ++nb) {
           mbar_wait(&tempty_bar[as], aphase ^ 1);
@@ -176,12 +191,15 @@ umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
                                           : make_sdesc_sw128(a_addr + k * (UK * 2), 16, 1024);
               const uint64_t bdesc = B_MN ? make_sdesc_sw128(b_addr + k * (UK * 128), BOX_MN_BYTES, 1024)
                                           : make_sdesc_sw128(b_addr + k * (UK * 2), 16, 1024);
-              mma_bf16_ss(tmem_d, adesc, bdesc, idesc, (uint32_t)(kb > t.kb0 || k > 0));
+              if (PAIR) mma_bf16_ss_pair(tmem_d, adesc, bdesc, idesc, (uint32_t)(kb > t.kb0 || k > 0));
+              else mma_bf16_ss(tmem_d, adesc, bdesc, idesc, (uint32_t)(kb > t.kb0 || k > 0));
             }
-            mma_commit(&empty_bar[stage]);          // frees the smem slot once these MMAs retire
+            // frees the smem slot (in both CTAs of a pair) once these MMAs retire
+            if (PAIR) mma_commit_pair(&empty_bar[stage]); else mma_commit(&empty_bar[stage]);
             if (++stage == STAGES) { stage = 0; phase ^= 1; }
           }
-          mma_commit(&tfull_bar[as]);               // accumulator tile complete
+          // accumulator tile complete (each CTA of a pair reads its own 128 rows from its own TMEM)
+          if (PAIR) mma_commit_pair(&tfull_bar[as]); else mma_commit(&tfull_bar[as]);
           as ^= 1; if (as == 0) aphase ^= 1;
         }
       }
@@ -196,10 +214,11 @@ umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
     const int gt = (int)threadIdx.x - 128 - half * 128;   // thread index inside this column-half group (0..127)
     int as = 0; uint32_t aphase = 0;
     uint32_t store_seq = 0;                         // MODE_CE_BWD: staging box toggle
-    for (int u = blockIdx.x; u < num_units; u += gridDim.x) {
+    for (int u = cid; u < num_units; u += ncl) {
       const Unit t = decode_unit(p, u);
-      const int mb = t.mb, s = t.s, nb0 = t.nb0, nb1 = t.nb1;
-      const long long row = (long long)mb * BM + trow;
+      const int s = t.s, nb0 = t.nb0, nb1 = t.nb1;
+      const int m0 = (t.mb * NC + crank) * BM;
+      const long long row = (long long)m0 + trow;
       const bool row_ok = row < p.M;
 
       // per-row state for the cross-entropy epilogues
@@ -346,7 +365,7 @@ umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
               fence_proxy_async_smem();              // generic-proxy writes -> visible to the TMA engine
               named_bar_sync(1 + half, 128);
               if (gt == 0) {
-                tma_store_2d(&tmD, box, col0, mb * BM);
+                tma_store_2d(&tmD, box, col0, m0);
                 bulk_commit();
               }
               ++store_seq;
@@ -354,7 +373,10 @@ umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
           }
         }
         tc_fence_before();
-        mbar_arrive(&tempty_bar[as]);               // 256 arrivals hand the accumulator stage back to the MMA warp
+        __syncwarp();
+        if (lane == 0) {                            // one arrival per warp hands the accumulator stage back to the MMA thread
+          if (PAIR) mbar_arrive_leader(&tempty_bar[as]); else mbar_arrive(&tempty_bar[as]);
+        }
         as ^= 1; if (as == 0) aphase ^= 1;
       }
 
@@ -368,8 +390,11 @@ umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
 
   if (MODE == MODE_CE_BWD && (threadIdx.x == 128 || threadIdx.x == 256)) bulk_wait_all();   // last stores have landed   // the last tile's store has landed
   tc_fence_before();
-  __syncthreads();
-  if (warp == 2) { tc_fence_after(); tmem_dealloc<TMEM_COLS>(tmem_base); }
+  if (PAIR) cluster_sync_all(); else __syncthreads();    // neither CTA of a pair may leave while the other still needs it
+  if (warp == 2) {
+    tc_fence_after();
+    if (PAIR) tmem_dealloc_pair<TMEM_COLS>(tmem_base); else tmem_dealloc<TMEM_COLS>(tmem_base);
+  }
 }
 
 // merge the per-split (max, sumexp) partials of each row into lse[row]
@@ -469,16 +494,43 @@ int num_sms() {
   return n;
 }
 
-template <int MODE, int A_MN, int B_MN>
-int launch(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& td, const Params& p, cudaStream_t stream) {
-  auto kern = umma_kernel<MODE, A_MN, B_MN>;
-  constexpr int SMEM_BYTES = smem_bytes_for(MODE);
+// CTA pairs (tcgen05 cta_group::2, M = 256 per MMA) for the forward and the plain GEMMs; the dlogits kernel, whose
+// epilogue is the heavier side, measured faster with independent CTAs (profiles/). B2_PAIR=0 / B2_PAIR=1 in the
+// environment forces one shape everywhere (A/B measurements).
+bool use_pair(int mode) {
+  static const int forced = [] { const char* e = getenv("B2_PAIR"); return e == nullptr ? -1 : (e[0] != '0'); }();
+  if (forced >= 0) return forced != 0;
+  return mode != MODE_CE_BWD;
+}
+// rows of A covered by one work unit
+int rows_per_unit(int mode) { return use_pair(mode) ? 2 * BM : BM; }
+// CTAs (single mode) or CTA pairs (pair mode) that run concurrently
+int num_workers(int mode) { return use_pair(mode) ? num_sms() / 2 : num_sms(); }
+
+template <int MODE, int A_MN, int B_MN, bool PAIR>
+int launch_impl(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& td, const Params& p, cudaStream_t stream) {
+  auto kern = umma_kernel<MODE, A_MN, B_MN, PAIR>;
+  constexpr int SMEM_BYTES = smem_bytes_for(MODE, PAIR);
   B2_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
   const int units = p.num_m_blocks * p.n_splits * p.k_splits;
-  const int grid = units < num_sms() ? units : num_sms();
-  kern<<<grid, NUM_THREADS, SMEM_BYTES, stream>>>(ta, tb, td, p);
-  B2_CHECK_CUDA(cudaGetLastError());
+  const int workers = units < num_workers(MODE) ? units : num_workers(MODE);
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = dim3((unsigned)(workers * (PAIR ? 2 : 1)));
+  cfg.blockDim = dim3(NUM_THREADS);
+  cfg.dynamicSmemBytes = SMEM_BYTES;
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = PAIR ? 2 : 1; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr; cfg.numAttrs = 1;
+  B2_CHECK_CUDA(cudaLaunchKernelEx(&cfg, kern, ta, tb, td, p));
   return B2_OK;
+}
+
+template <int MODE, int A_MN, int B_MN>
+int launch(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& td, const Params& p, cudaStream_t stream) {
+  return use_pair(MODE) ? launch_impl<MODE, A_MN, B_MN, true>(ta, tb, td, p, stream)
+                    : launch_impl<MODE, A_MN, B_MN, false>(ta, tb, td, p, stream);
 }
 
 // operand [rows = M or N extent, K] -> tensor map; K-major: memory is [extent, ld] with K contiguous;
@@ -556,15 +608,15 @@ extern "C" int b2_gemm_bf16(const void* A, int a_mn_major, long long lda, const 
   CUtensorMap ta, tb;
   int rc;
   if ((rc = make_operand_tmap(&ta, A, a_mn_major, M, K, lda, BM, "b2_gemm_bf16 A")) != B2_OK) return rc;
-  if ((rc = make_operand_tmap(&tb, B, b_mn_major, N, K, ldb, BN, "b2_gemm_bf16 B")) != B2_OK) return rc;
+  if ((rc = make_operand_tmap(&tb, B, b_mn_major, N, K, ldb, use_pair(MODE_GEMM) ? BN / 2 : BN, "b2_gemm_bf16 B")) != B2_OK) return rc;
   Params p{};
   p.M = M; p.N = N; p.K = K;
-  p.num_m_blocks = (M + BM - 1) / BM; p.num_n_blocks = (N + BN - 1) / BN; p.num_k_blocks = (K + BK - 1) / BK;
+  p.num_m_blocks = (M + rows_per_unit(MODE_GEMM) - 1) / rows_per_unit(MODE_GEMM); p.num_n_blocks = (N + BN - 1) / BN; p.num_k_blocks = (K + BK - 1) / BK;
   p.n_splits = p.num_n_blocks;
   p.n_fastest = p.num_n_blocks <= 8;     // few column blocks: let the CTAs that share an A row-block run side by side
   p.k_splits = 1;
   if (workspace != nullptr && workspace_bytes >= b2_gemm_workspace_bytes(M, N) && b2_aligned(workspace, 16))
-    p.k_splits = auto_k_splits(p.num_m_blocks * p.num_n_blocks, p.num_k_blocks, num_sms());
+    p.k_splits = auto_k_splits(p.num_m_blocks * p.num_n_blocks, p.num_k_blocks, num_workers(MODE_GEMM));
   p.ws = static_cast<float*>(workspace); p.ldws = ((long long)N + 3) / 4 * 4;
   p.C = C; p.ldc = ldc; p.c_dtype = c_dtype; p.accumulate = accumulate;
   static const bool noepi = getenv("B2_DEBUG_NOEPI") != nullptr;     // profiling only: mainloop ceiling without stores
@@ -603,15 +655,15 @@ extern "C" int b2_lmhead_ce_fwd(const void* H, long long ldh, const void* W, lon
     CUtensorMap ta, tb;
     int rc;
     if ((rc = make_operand_tmap(&ta, H, 0, N, D, ldh, BM, "b2_lmhead_ce_fwd H")) != B2_OK) return rc;
-    if ((rc = make_operand_tmap(&tb, W, 0, V, D, ldw, BN, "b2_lmhead_ce_fwd W")) != B2_OK) return rc;
+    if ((rc = make_operand_tmap(&tb, W, 0, V, D, ldw, use_pair(MODE_CE_FWD) ? BN / 2 : BN, "b2_lmhead_ce_fwd W")) != B2_OK) return rc;
     Params p{};
     p.M = (int)N; p.N = V; p.K = D;
-    p.num_m_blocks = (int)((N + BM - 1) / BM); p.num_n_blocks = (V + BN - 1) / BN; p.num_k_blocks = (D + BK - 1) / BK;
-    p.n_splits = choose_splits(p.num_m_blocks, p.num_n_blocks, num_sms());
+    p.num_m_blocks = (int)((N + rows_per_unit(MODE_CE_FWD) - 1) / rows_per_unit(MODE_CE_FWD)); p.num_n_blocks = (V + BN - 1) / BN; p.num_k_blocks = (D + BK - 1) / BK;
+    p.n_splits = choose_splits(p.num_m_blocks, p.num_n_blocks, num_workers(MODE_CE_FWD));
     p.k_splits = 1; p.n_fastest = 0;
     p.labels = labels; p.shift_T = shift_T; p.ignore_index = ignore_index; p.row0 = 0;
     p.bias = bias; p.round_bf16 = round_logits_bf16;
-    p.part = static_cast<float2*>(workspace); p.part_stride = (long long)p.num_m_blocks * BM; p.zt = zt;
+    p.part = static_cast<float2*>(workspace); p.part_stride = (N + BM - 1) / BM * BM; p.zt = zt;
     if ((rc = launch<MODE_CE_FWD, 0, 0>(ta, tb, ta, p, stream)) != B2_OK) return rc;
     ce_combine_kernel<<<(unsigned)((N + 255) / 256), 256, 0, stream>>>(p.part, p.part_stride, 2 * p.n_splits, N, lse);
     B2_CHECK_CUDA(cudaGetLastError());
@@ -632,10 +684,10 @@ extern "C" int b2_lmhead_ce_bwd_dlogits(const void* H, long long ldh, const void
   CUtensorMap ta, tb;
   int rc;
   if ((rc = make_operand_tmap(&ta, H, 0, rows, D, ldh, BM, "b2_lmhead_ce_bwd_dlogits H")) != B2_OK) return rc;
-  if ((rc = make_operand_tmap(&tb, W, 0, V, D, ldw, BN, "b2_lmhead_ce_bwd_dlogits W")) != B2_OK) return rc;
+  if ((rc = make_operand_tmap(&tb, W, 0, V, D, ldw, use_pair(MODE_CE_BWD) ? BN / 2 : BN, "b2_lmhead_ce_bwd_dlogits W")) != B2_OK) return rc;
   Params p{};
   p.M = (int)rows; p.N = V; p.K = D;
-  p.num_m_blocks = (int)((rows + BM - 1) / BM); p.num_n_blocks = (V + BN - 1) / BN; p.num_k_blocks = (D + BK - 1) / BK;
+  p.num_m_blocks = (int)((rows + rows_per_unit(MODE_CE_BWD) - 1) / rows_per_unit(MODE_CE_BWD)); p.num_n_blocks = (V + BN - 1) / BN; p.num_k_blocks = (D + BK - 1) / BK;
   p.n_splits = p.num_n_blocks; p.k_splits = 1; p.n_fastest = 0;
   p.labels = labels; p.shift_T = shift_T; p.ignore_index = ignore_index; p.row0 = row0;
   p.bias = bias; p.round_bf16 = round_logits_bf16;
