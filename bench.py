@@ -139,10 +139,38 @@ def f1_roofline(torch, b200, model, device, peaks, iters=5):
     ms = sum(times) / len(times)
     flops = 6.0 * N * V * D
     achieved = flops / (ms * 1e-3) / 1e12
+    # the four launches of the family, each timed alone (2*N*V*D flop per launch)
+    from b200_train import ops
+    y = labels.reshape(-1)
+    Hd, Wd = H.detach(), Wl.detach()
+    r = ops.lmhead_ce_fwd(Hd, Wd, y, shift_T=SEQ)
+    ldd = (V + 7) // 8 * 8
+    dl = torch.empty(N, ldd, dtype=torch.bfloat16, device=device)
+    dH = torch.empty(N, D, dtype=torch.bfloat16, device=device)
+    dW = torch.empty(V, D, dtype=torch.bfloat16, device=device)
+    gs = torch.full((1,), 1.0 / N, device=device)
+    parts = {}
+    for name, fn in (("forward", lambda: ops.lmhead_ce_fwd(Hd, Wd, y, shift_T=SEQ)),
+                     ("dlogits", lambda: ops.lmhead_ce_bwd_dlogits(Hd, Wd, y, r.lse, gs, 0, N, dl, shift_T=SEQ)),
+                     ("dH", lambda: ops.gemm_bf16(dl, Wd, dH, N, D, V, b_mn_major=True)),
+                     ("dW", lambda: ops.gemm_bf16(dl, Hd, dW, V, D, N, a_mn_major=True, b_mn_major=True))):
+        ts = []
+        for it in range(iters + 1):
+            flush.fill_(it & 0xff)
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record(); fn(); e1.record()
+            torch.cuda.synchronize()
+            if it >= 1:
+                ts.append(e0.elapsed_time(e1))
+        t = sum(ts) / len(ts)
+        parts[name] = {"ms": t, "tflops": 2.0 * N * V * D / (t * 1e-3) / 1e12}
     return {"bound": "tensor", "achieved": achieved, "peak": peaks["bf16_tflops"], "unit": "TFLOP/s",
-            "frac": achieved / peaks["bf16_tflops"], "traffic": None,
-            "kernel": "umma_kernel (fused LM-head+CE fwd, dlogits recompute, dH and dW GEMMs)",
-            "ms": ms, "algorithmic_flops": flops, "peak_source": peaks["source"] + ", burst bf16 GEMM"}
+            "frac": achieved / peaks["bf16_tflops"],
+            "traffic": 3.13e9,   # dram read+write summed over the family's 4 launches, ncu --set full (profiles/README.md)
+            "kernel": "umma_kernel family per step: fused LM-head+CE forward, dlogits recompute, dH GEMM, dW GEMM "
+                      "(timed together through autograd; 6*N*V*D algorithmic flop, 8*N*V*D executed)",
+            "ms": ms, "algorithmic_flops": flops, "launches": parts,
+            "peak_source": peaks["source"] + ", burst bf16 GEMM"}
 
 
 def f3_roofline(torch, ops, device, peaks, n=1 << 27, iters=5):
@@ -163,7 +191,7 @@ def f3_roofline(torch, ops, device, peaks, n=1 << 27, iters=5):
     ms = sum(times) / len(times)
     gbs = 14.0 * n / (ms * 1e-3) / 1e9
     return {"bound": "hbm", "achieved": gbs, "peak": peaks["hbm_gbs"], "unit": "GB/s", "frac": gbs / peaks["hbm_gbs"],
-            "traffic": None, "kernel": "adamw_kernel (pure bf16, n=2^27)", "ms": ms}
+            "traffic": 1.823e9, "kernel": "adamw_kernel (pure bf16, n=2^27; 14 B/element = 1.879e9 algorithmic bytes)", "ms": ms}
 
 
 def run_ours(args):
