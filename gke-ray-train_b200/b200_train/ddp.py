@@ -30,9 +30,17 @@ def get_device():
     return torch.device("cuda", int(os.environ.get("LOCAL_RANK", "0")) % torch.cuda.device_count())
 
 
+class _Bucket:
+    """A contiguous element range of one flat gradient buffer, reduced by one kernel launch."""
+    __slots__ = ("buf", "offset", "numel", "nparams", "pending")
+
+    def __init__(self, buf, offset, numel, nparams):
+        self.buf, self.offset, self.numel, self.nparams, self.pending = buf, offset, numel, nparams, nparams
+
+
 class DistributedDataParallel(nn.Module):
     def __init__(self, module, device_ids=None, output_device=None, process_group=None, broadcast_buffers=True,
-                 shard_optimizer=False, **unused):
+                 bucket_cap_mb=None, overlap=True, shard_optimizer=False, **unused):
         super().__init__()
         if not dist.is_initialized():
             raise B2Error("DistributedDataParallel needs an initialised torch.distributed process group")
@@ -55,29 +63,97 @@ class DistributedDataParallel(nn.Module):
             dist.broadcast(buf.data, src=0, group=process_group)
             buf.comm = self.comm
             buf.reduced_sumsq = None
+            buf._sumsq_store = torch.empty(self.world_size, dtype=torch.float32, device=device)
         for b in module.buffers():
             if b.is_cuda:
                 dist.broadcast(b, src=0, group=process_group)
         self.require_backward_grad_sync = True
         self._callback_queued = False
+        # Buckets, like torch DDP's ($SP/torch/nn/parallel/distributed.py:831-833), but as ranges of the
+        # flat buffer: parameters are laid out in registration order and their gradients arrive roughly in reverse, so
+        # buckets are cut from the END of each buffer and launched in that fixed order on a side stream while the rest
+        # of backward still runs.
+        # (B2_DDP_OVERLAP / B2_DDP_BUCKET_MB / B2_DDP_MAX_BLOCKS override the arguments for measurements)
+        self.overlap = bool(int(os.environ.get("B2_DDP_OVERLAP", int(bool(overlap)))))
+        # measured on GPT-2 124M / 2 GPUs (profiles/README.md): 100 MiB buckets on <= 96 CTAs beat torch's 25 MiB default
+        bucket_cap_mb = float(os.environ.get("B2_DDP_BUCKET_MB", 100 if bucket_cap_mb is None else bucket_cap_mb))
+        self._overlap_blocks = int(os.environ.get("B2_DDP_MAX_BLOCKS", 96))
+        cap_bytes = int(bucket_cap_mb * 1024 * 1024) if self.overlap else (1 << 62)      # no overlap: one launch per buffer
+        self._buckets, self._bucket_of = [], {}
+        for buf in self.buffers:
+            esize = buf.data.element_size()
+            end = buf.numel
+            members = []
+            for i in range(len(buf.params) - 1, -1, -1):
+                members.append(i)
+                start = buf.offsets[i]
+                if (end - start) * esize >= cap_bytes or i == 0:
+                    b = _Bucket(buf, start, end - start, len(members))
+                    for j in members:
+                        self._bucket_of[id(buf.params[j])] = len(self._buckets)
+                    self._buckets.append(b)
+                    end, members = start, []
+        self._next_bucket = 0
+        self._comm_stream = torch.cuda.Stream(device=device) if self.overlap else None
         for p in params:
             p.register_post_accumulate_grad_hook(self._on_grad)
 
     # ------------------------------------------------------------------ backward-side plumbing
-    def _on_grad(self, _p):
-        if self._callback_queued or not self.require_backward_grad_sync:
+    def _launch_bucket(self, b, tail=False):
+        """Peer-memory all-reduce of one bucket. With overlap it runs on the side stream, ordered after everything the
+        backward stream has enqueued so far, on a capped grid so it shares the SMs with the remaining backward kernels."""
+        first = self._next_bucket == 0 or b.buf is not self._buckets[self._next_bucket - 1].buf
+        mode = 1 if first else 2          # sum-of-squares slots: restart on a buffer's first bucket, then keep adding
+        if self.overlap:
+            ev = torch.cuda.Event()
+            ev.record(torch.cuda.current_stream())
+            self._comm_stream.wait_event(ev)
+            with torch.cuda.stream(self._comm_stream):
+                self.comm.allreduce_(b.buf.grad, want_sumsq=mode, offset=b.offset, numel=b.numel,
+                                     max_blocks=0 if tail else self._overlap_blocks)      # nothing left to overlap with: whole GPU
+        else:
+            self.comm.allreduce_(b.buf.grad, want_sumsq=mode, offset=b.offset, numel=b.numel)
+
+    def _launch_ready(self, force=False):
+        while self._next_bucket < len(self._buckets):
+            b = self._buckets[self._next_bucket]
+            if b.pending > 0 and not force:
+                break
+            last_of_buf = (self._next_bucket + 1 == len(self._buckets)
+                           or self._buckets[self._next_bucket + 1].buf is not b.buf)
+            self._launch_bucket(b, tail=force)
+            self._next_bucket += 1
+            if last_of_buf:
+                # the W per-rank partials of this buffer are complete once this launch retires: keep a copy, the slots
+                # are reused by the next buffer / step
+                stream = self._comm_stream if self.overlap else torch.cuda.current_stream()
+                with torch.cuda.stream(stream):
+                    b.buf._sumsq_store.copy_(self.comm._parts)
+                b.buf.reduced_sumsq = b.buf._sumsq_store
+
+    def _on_grad(self, p):
+        if not self.require_backward_grad_sync:
             return
-        self._callback_queued = True
-        Variable._execution_engine.queue_callback(self._finalize_backward)
+        if not self._callback_queued:
+            self._callback_queued = True
+            Variable._execution_engine.queue_callback(self._finalize_backward)
+        k = self._bucket_of.get(id(p))
+        if k is not None:
+            self._buckets[k].pending -= 1
+            if self.overlap:
+                self._launch_ready()
 
     def _finalize_backward(self):
         """Runs once per backward pass, after the last gradient has been accumulated."""
         self._callback_queued = False
         for buf in self.buffers:
-            if buf.install_grads():
-                pass  # a stray .grad was copied into the flat buffer
-            parts = self.comm.allreduce_(buf.grad, want_sumsq=True, scatter_only=False)
-            buf.reduced_sumsq = parts.clone()      # `world` floats; clip_grad_norm_ reuses them instead of re-reading
+            buf.install_grads()            # a stray .grad (allocated by autograd after a foreign zero_grad) is copied in
+        self._launch_ready(force=True)     # whatever is left (all of it without overlap; unused parameters' buckets)
+        if self.overlap:
+            torch.cuda.current_stream().wait_stream(self._comm_stream)
+        self._next_bucket = 0
+        for b in self._buckets:
+            b.pending = b.nparams
 
     # ------------------------------------------------------------------ nn.Module surface
     def forward(self, *args, **kwargs):

@@ -120,14 +120,16 @@ class PeerComm:
              ctypes.byref(b), ctypes.byref(e))
         return b.value, e.value
 
-    def allreduce_(self, t, scale=None, want_sumsq=False, scatter_only=False):
-        """In-place mean (scale = 1/world by default) over ranks of the flat symmetric tensor `t`."""
+    def allreduce_(self, t, scale=None, want_sumsq=False, scatter_only=False, offset=0, numel=None, max_blocks=0):
+        """In-place mean (scale = 1/world by default) over ranks of elements [offset, offset+numel) of the flat
+        symmetric tensor `t`. want_sumsq: False / True (restart the sum-of-squares slots) / 2 (keep adding to them)."""
         sb, off = self._symm_of(t)
         self.epoch += 1
+        numel = t.numel() - offset if numel is None else numel
         with torch.cuda.device(self.device):
-            call("b2_peer_allreduce", sb.ptr_table(off), self._flag_table, self.world, self.rank, 0, t.numel(),
+            call("b2_peer_allreduce", sb.ptr_table(off), self._flag_table, self.world, self.rank, int(offset), int(numel),
                  dtype_code(t.dtype), float(1.0 / self.world if scale is None else scale), self.epoch,
-                 int(bool(want_sumsq)), int(bool(scatter_only)), stream_ptr())
+                 int(want_sumsq), int(bool(scatter_only)), int(max_blocks), stream_ptr())
         return self._parts if want_sumsq else None
 
     def allgather_(self, t):

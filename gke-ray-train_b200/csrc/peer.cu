@@ -234,9 +234,10 @@ void slice_of(size_t nvec, int world, int rank, size_t& v0, size_t& v1) {
   v1 = v0 + per < nvec ? v0 + per : nvec;
 }
 
-unsigned peer_grid(size_t nvec_slice) {
+unsigned peer_grid(size_t nvec_slice, int max_blocks) {
   size_t blocks = (nvec_slice + 511) / 512;
-  const size_t cap = (size_t)B2_NUM_SMS * 2;     // 2 x 512 threads per SM: enough loads in flight to cover NVLink latency
+  size_t cap = (size_t)B2_NUM_SMS * 2;           // 2 x 512 threads per SM: enough loads in flight to cover NVLink latency
+  if (max_blocks > 0 && (size_t)max_blocks < cap) cap = (size_t)max_blocks;   // overlapped with compute: leave SMs free
   if (blocks > cap) blocks = cap;
   if (blocks == 0) blocks = 1;
   return (unsigned)blocks;
@@ -282,7 +283,7 @@ extern "C" int b2_symm_free(void* dptr) {
 // ---- collectives ------------------------------------------------------------------------------------------------
 extern "C" int b2_peer_allreduce(void* const* peer_bufs, uint32_t* const* peer_flags, int world, int rank,
                                  size_t offset_elems, size_t n, int dtype, float scale, unsigned epoch, int want_sumsq,
-                                 int scatter_only, cudaStream_t stream) {
+                                 int scatter_only, int max_blocks, cudaStream_t stream) {
   B2_REQUIRE(dtype == B2_F32 || dtype == B2_BF16, "b2_peer_allreduce: dtype must be 0 (f32) or 1 (bf16)");
   B2_REQUIRE(rank >= 0 && rank < world, "b2_peer_allreduce: rank %d outside world %d", rank, world);
   const size_t es = b2_dtype_size(dtype), per_vec = 16 / es;
@@ -292,8 +293,8 @@ extern "C" int b2_peer_allreduce(void* const* peer_bufs, uint32_t* const* peer_f
   if (rc != B2_OK) return rc;
   size_t v0, v1;
   slice_of(n / per_vec, world, rank, v0, v1);
-  if (want_sumsq) peer_zero_sumsq_kernel<<<1, 32, 0, stream>>>(pp.flags[rank]);
-  const unsigned grid = peer_grid(v1 - v0);
+  if (want_sumsq == 1) peer_zero_sumsq_kernel<<<1, 32, 0, stream>>>(pp.flags[rank]);   // 2 = keep adding to the slots
+  const unsigned grid = peer_grid(v1 - v0, max_blocks);
 #define B2_PEER_CASE(DT, W)                                                                                        \
   if (dtype == DT && world == W) {                                                                                 \
     if (scatter_only) peer_allreduce_kernel<DT, W, true><<<grid, 512, 0, stream>>>(pp, rank, v0, v1, scale, epoch, want_sumsq); \
@@ -321,7 +322,7 @@ extern "C" int b2_peer_allgather(void* const* peer_bufs, uint32_t* const* peer_f
   if (rc != B2_OK) return rc;
   size_t v0, v1;
   slice_of(n / per_vec, world, rank, v0, v1);
-  const unsigned grid = peer_grid(v1 - v0);
+  const unsigned grid = peer_grid(v1 - v0, 0);
 #define B2_AG_CASE(W)                                                                       \
   if (world == W) {                                                                         \
     peer_allgather_kernel<W><<<grid, 512, 0, stream>>>(pp, rank, v0, v1, epoch);            \

@@ -165,7 +165,9 @@ size_t b2_gemm_workspace_bytes(int M, int N);
  *   buf[i] <- round_dtype(scale * sum_k buf_k[i]) on all ranks (scale = 1/world for DDP's mean), bit-identical
  *   everywhere. want_sumsq != 0 additionally leaves, in each rank's flag block, float slot 32 + k = sum of squares
  *   of the reduced values of rank k's slice (k = 0..world-1) — feed those `world` floats to b2_clip_coef.
+ *   want_sumsq = 2 keeps adding to the slots instead of restarting them (several bucket calls of one backward pass).
  *   scatter_only != 0 stores the reduced slice of rank r on rank r only (reduce-scatter; see b2_peer_slice).
+ *   max_blocks > 0 caps the grid (a bucket reduced while backward kernels still run should not occupy every SM).
  * b2_peer_allgather: pushes this rank's slice of the buffer to every peer (used for updated parameters).
  * `epoch` must increase by one on every collective call, identically on all ranks (start at 1).
  * Every rank must enqueue the same sequence of calls; the kernels wait for one another inside the GPU, so each
@@ -177,7 +179,7 @@ int b2_symm_close(void* dptr);
 int b2_symm_free(void* dptr);
 int b2_peer_allreduce(void* const* peer_bufs, uint32_t* const* peer_flags, int world, int rank, size_t offset_elems,
                       size_t n, int dtype, float scale, unsigned epoch, int want_sumsq, int scatter_only,
-                      b2_stream_t stream);
+                      int max_blocks, b2_stream_t stream);
 int b2_peer_allgather(void* const* peer_bufs, uint32_t* const* peer_flags, int world, int rank, size_t offset_elems,
                       size_t n, int dtype, unsigned epoch, b2_stream_t stream);
 int b2_peer_slice(size_t n, int dtype, int world, int rank, size_t* begin, size_t* end);

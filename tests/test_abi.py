@@ -60,8 +60,8 @@ def test_bad_arguments_are_rejected_without_a_gpu(lib):
     assert L.b2_ce_rows_fwd(16, 0, 4, 0, 0, 16, 0, -100, 16, 16, 16, 16, None, None) == -1
     assert L.b2_lmhead_ce_fwd(16, 8, 16, 8, None, 16, 10, 8, 8, 3, -100, 1, 16, 0, 16, 16, 16, 16, None, None) == -1
     assert b"multiple of shift_T" in L.b2_last_error()
-    assert L.b2_peer_allreduce(None, None, 9, 0, 0, 64, 1, 0.5, 1, 0, 0, None) == -1
-    assert L.b2_peer_allreduce(None, None, 2, 2, 0, 64, 1, 0.5, 1, 0, 0, None) == -1
+    assert L.b2_peer_allreduce(None, None, 9, 0, 0, 64, 1, 0.5, 1, 0, 0, 0, None) == -1
+    assert L.b2_peer_allreduce(None, None, 2, 2, 0, 64, 1, 0.5, 1, 0, 0, 0, None) == -1
     with pytest.raises(lib.B2Error):
         lib.call("b2_scale", None, 8, 0, None, None)
 

@@ -273,7 +273,7 @@ def test_peer_allreduce_single_gpu_emulation(b200):
         bt = (ctypes.c_void_p * world)(*[b.data_ptr() for b in bufs])
         ft = (ctypes.c_void_p * world)(*[f.data_ptr() for f in flags])
         for r in range(world):
-            _lib.call("b2_peer_allreduce", bt, ft, world, r, 0, n, _lib.dtype_code(dtype), 1.0 / world, epoch, 1, 0,
+            _lib.call("b2_peer_allreduce", bt, ft, world, r, 0, n, _lib.dtype_code(dtype), 1.0 / world, epoch, 1, 0, 0,
                       torch.cuda.current_stream().cuda_stream)
         torch.cuda.synchronize()
         acc = torch.zeros(n, dtype=torch.float32, device=dev())
@@ -292,7 +292,7 @@ def test_peer_allreduce_single_gpu_emulation(b200):
         bufs2 = [o.clone() for o in orig]
         bt2 = (ctypes.c_void_p * world)(*[b.data_ptr() for b in bufs2])
         for r in range(world):
-            _lib.call("b2_peer_allreduce", bt2, ft, world, r, 0, n, _lib.dtype_code(dtype), 1.0 / world, epoch, 0, 1,
+            _lib.call("b2_peer_allreduce", bt2, ft, world, r, 0, n, _lib.dtype_code(dtype), 1.0 / world, epoch, 0, 1, 0,
                       torch.cuda.current_stream().cuda_stream)
         for r in range(world):
             _lib.call("b2_peer_allgather", bt2, ft, world, r, 0, n, _lib.dtype_code(dtype), epoch,
