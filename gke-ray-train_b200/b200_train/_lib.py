@@ -65,6 +65,8 @@ _SIGS = {
     "b2_symm_free": (c_int, [c_void_p]),
     "b2_peer_allreduce": (c_int, [c_void_p, c_void_p, c_int, c_int, c_size_t, c_size_t, c_int, c_float, ctypes.c_uint,
                                   c_int, c_int, c_int, c_void_p]),
+    "b2_peer_allreduce_mc": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_size_t, c_size_t, c_int, c_float,
+                                     ctypes.c_uint, c_int, c_int, c_int, c_void_p]),
     "b2_peer_allgather": (c_int, [c_void_p, c_void_p, c_int, c_int, c_size_t, c_size_t, c_int, ctypes.c_uint, c_void_p]),
     "b2_peer_slice": (c_int, [c_size_t, c_int, c_int, c_int, c_void_p, c_void_p]),
 }
@@ -80,7 +82,7 @@ EXPORTS = tuple(_SIGS)
 launch_count = 0
 _LAUNCHES = {"b2_adamw": 1, "b2_adamw_grouped": 1, "b2_sumsq": 1, "b2_sumsq_static": 1, "b2_clip_coef": 1, "b2_scale": 1, "b2_ce_rows_fwd": 2,
              "b2_ce_rows_bwd": 1, "b2_lmhead_ce_fwd": 3, "b2_lmhead_ce_bwd_dlogits": 1, "b2_gemm_bf16": 1,  # (+1 reduce launch when split-K kicks in)
-             "b2_peer_allreduce": 1, "b2_peer_allgather": 1}
+             "b2_peer_allreduce": 1, "b2_peer_allreduce_mc": 1, "b2_peer_allgather": 1}
 
 
 def call(name, *args):

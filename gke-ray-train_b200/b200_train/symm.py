@@ -83,6 +83,63 @@ class SymmetricBuffer:
         _lib.lib.b2_symm_free(self.local_ptr)
 
 
+class TorchSymmetricBuffer:
+    """Same interface as SymmetricBuffer, but the allocation, the peer mappings and — where the fabric supports it — an
+    NVLS multicast address come from torch.distributed._symmetric_memory (VMM allocations instead of cudaMalloc + IPC).
+    This is bootstrap plumbing only; the collectives that run on these pointers are still our kernels."""
+
+    def __init__(self, nbytes, device, group=None):
+        import torch.distributed._symmetric_memory as symm_mem
+        self.group = group
+        self.world = dist.get_world_size(group)
+        self.rank = dist.get_rank(group)
+        self.device = device
+        self.nbytes = (nbytes + 255) // 256 * 256
+        self._t = symm_mem.empty(self.nbytes, dtype=torch.uint8, device=device)
+        self._t.zero_()
+        self._hdl = symm_mem.rendezvous(self._t, group if group is not None else dist.group.WORLD)
+        self.ptrs = [int(p) for p in self._hdl.buffer_ptrs]
+        self.local_ptr = self.ptrs[self.rank]
+        self.mc_ptr = int(self._hdl.multicast_ptr) or None
+        self._closed = False
+
+    def tensor(self, dtype, numel, byte_offset=0):
+        nbytes = numel * torch.empty((), dtype=dtype).element_size()
+        if byte_offset + nbytes > self.nbytes:
+            raise B2Error("symmetric buffer too small for the requested view")
+        t = self._t[byte_offset:byte_offset + nbytes].view(dtype)
+        t._b2_symm = (self, byte_offset)
+        return t
+
+    def ptr_table(self, byte_offset=0):
+        return (ctypes.c_void_p * self.world)(*[p + byte_offset for p in self.ptrs])
+
+    def close(self):
+        if not self._closed:
+            self._closed = True
+            torch.cuda.synchronize(self.device)
+            dist.barrier(group=self.group)
+            self._hdl = None
+            self._t = None
+
+
+def _pick_backend():
+    """B2_SYMM_BACKEND=ipc | torch. Default: torch's symmetric memory when it reports NVLS multicast support (needed for
+    the in-switch reduction), else plain CUDA IPC."""
+    import os
+    forced = os.environ.get("B2_SYMM_BACKEND")
+    if forced in ("ipc", "torch"):
+        return forced
+    try:
+        import torch.distributed._symmetric_memory as symm_mem
+        from torch._C._autograd import DeviceType
+        if symm_mem._SymmetricMemory.has_multicast_support(DeviceType.CUDA, torch.cuda.current_device()):
+            return "torch"
+    except Exception:  # noqa: BLE001 - any failure here just means "no multicast allocator"
+        pass
+    return "ipc"
+
+
 class PeerComm:
     """Per-process handle for the peer-memory collectives: flag block, epoch counter, slice arithmetic."""
 
@@ -93,6 +150,10 @@ class PeerComm:
         if self.world > 8:
             raise B2Error("peer-memory collectives support up to 8 ranks (one NVSwitch domain)")
         self.device = device
+        self.backend = _pick_backend()
+        # in-switch reduction pays off once there are more than two ranks (B2_PEER_NVLS=0/1 overrides)
+        import os
+        self.use_nvls = bool(int(os.environ.get("B2_PEER_NVLS", int(self.world > 2))))
         self.flags = SymmetricBuffer(_lib.lib.b2_peer_flags_bytes(), device, group)
         self.epoch = 0
         self._flag_table = self.flags.ptr_table()
@@ -103,7 +164,8 @@ class PeerComm:
     def alloc(self, numel, dtype, device):
         """Allocator hook for flat.flatten_params: tensors that live in symmetric memory."""
         esize = torch.empty((), dtype=dtype).element_size()
-        sb = SymmetricBuffer(max(numel * esize, 256), device, self.group)
+        cls = TorchSymmetricBuffer if self.backend == "torch" else SymmetricBuffer
+        sb = cls(max(numel * esize, 256), device, self.group)
         self.buffers.append(sb)
         return sb.tensor(dtype, numel)
 
@@ -126,10 +188,17 @@ class PeerComm:
         sb, off = self._symm_of(t)
         self.epoch += 1
         numel = t.numel() - offset if numel is None else numel
+        sc = float(1.0 / self.world if scale is None else scale)
+        mc = getattr(sb, "mc_ptr", None)
         with torch.cuda.device(self.device):
-            call("b2_peer_allreduce", sb.ptr_table(off), self._flag_table, self.world, self.rank, int(offset), int(numel),
-                 dtype_code(t.dtype), float(1.0 / self.world if scale is None else scale), self.epoch,
-                 int(want_sumsq), int(bool(scatter_only)), int(max_blocks), stream_ptr())
+            if mc and self.use_nvls:
+                call("b2_peer_allreduce_mc", mc + off, sb.ptr_table(off), self._flag_table, self.world, self.rank,
+                     int(offset), int(numel), dtype_code(t.dtype), sc, self.epoch, int(want_sumsq),
+                     int(bool(scatter_only)), int(max_blocks), stream_ptr())
+            else:
+                call("b2_peer_allreduce", sb.ptr_table(off), self._flag_table, self.world, self.rank, int(offset),
+                     int(numel), dtype_code(t.dtype), sc, self.epoch, int(want_sumsq), int(bool(scatter_only)),
+                     int(max_blocks), stream_ptr())
         return self._parts if want_sumsq else None
 
     def allgather_(self, t):

@@ -345,3 +345,167 @@ extern "C" int b2_peer_slice(size_t n, int dtype, int world, int rank, size_t* b
   *end = v1 * per_vec;
   return B2_OK;
 }
+
+// ---------------------------------------------------------------------------------------------------------------------
+// Measurement aid (tools/peer_probe.py, not part of the documented ABI): raw peer copy in one direction with a chosen
+// load flavour, unroll and grid, to find out what the NVLink path sustains from a kernel.
+//   mode 0: remote read  -> local write      mode 1: local read -> remote write
+//   flavour 0: ld.relaxed.sys   1: plain ld.global   2: ld.volatile
+namespace {
+template <int U, int FLAVOUR>
+__global__ void __launch_bounds__(512) peer_copy_probe_kernel(const uint4* __restrict__ src, uint4* __restrict__ dst, size_t nvec) {
+  const size_t stride = (size_t)gridDim.x * blockDim.x;
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < nvec; i += stride * U) {
+    uint4 v[U];
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const size_t j = i + (size_t)u * stride;
+      if (j < nvec) {
+        if (FLAVOUR == 0) v[u] = ld_peer(src + j);
+        else if (FLAVOUR == 1) v[u] = src[j];
+        else asm volatile("ld.volatile.global.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(v[u].x), "=r"(v[u].y), "=r"(v[u].z), "=r"(v[u].w) : "l"(src + j));
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const size_t j = i + (size_t)u * stride;
+      if (j < nvec) dst[j] = v[u];
+    }
+  }
+}
+}  // namespace
+
+extern "C" int b2_debug_peer_copy(const void* src, void* dst, size_t bytes, int unroll, int flavour, int blocks, cudaStream_t stream) {
+  const size_t nvec = bytes / 16;
+#define B2_PROBE(U, F) if (unroll == U && flavour == F) { peer_copy_probe_kernel<U, F><<<blocks, 512, 0, stream>>>(static_cast<const uint4*>(src), static_cast<uint4*>(dst), nvec); B2_CHECK_CUDA(cudaGetLastError()); return B2_OK; }
+  B2_PROBE(1, 0) B2_PROBE(2, 0) B2_PROBE(4, 0) B2_PROBE(8, 0)
+  B2_PROBE(1, 1) B2_PROBE(2, 1) B2_PROBE(4, 1) B2_PROBE(8, 1)
+  B2_PROBE(1, 2) B2_PROBE(4, 2)
+#undef B2_PROBE
+  b2_set_error("b2_debug_peer_copy: unsupported unroll/flavour");
+  return B2_ERR_INVALID;
+}
+
+// ---------------------------------------------------------------------------------------------------------------------
+// NVLS variant: the same in-place all-reduce, but the sum over ranks is formed INSIDE the NVSwitch.
+// `mc` is a multicast address that aliases the same offset of every rank's buffer: multimem.ld_reduce returns the
+// switch-side sum of all W copies (fp32 accumulation), multimem.st writes one value into all W copies. Each GPU then
+// sends and receives about n*s bytes in total instead of 2*(W-1)/W*n*s per direction, which is what lets the result
+// exceed the per-link roofline at W = 4 and 8 (reported against the same 2*(W-1)/W*n*s busbw formula, and labelled).
+namespace {
+
+template <int DT> struct McOps;
+template <> struct McOps<B2_BF16> {
+  __device__ __forceinline__ static uint4 ld_reduce(const void* p) {
+    uint4 r;
+    asm volatile("multimem.ld_reduce.relaxed.sys.global.add.acc::f32.v4.bf16x2 {%0,%1,%2,%3}, [%4];"
+                 : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p) : "memory");
+    return r;
+  }
+  __device__ __forceinline__ static void st(void* p, const uint4& v) {
+    asm volatile("multimem.st.relaxed.sys.global.v4.bf16x2 [%0], {%1,%2,%3,%4};"
+                 :: "l"(p), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
+  }
+};
+template <> struct McOps<B2_F32> {
+  __device__ __forceinline__ static uint4 ld_reduce(const void* p) {
+    uint4 r;
+    asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0,%1,%2,%3}, [%4];"
+                 : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p) : "memory");
+    return r;
+  }
+  __device__ __forceinline__ static void st(void* p, const uint4& v) {
+    asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1,%2,%3,%4};"
+                 :: "l"(p), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
+  }
+};
+
+template <int DT, bool SCATTER_ONLY>
+__global__ void __launch_bounds__(512) peer_allreduce_mc_kernel(const __grid_constant__ PeerPtrs pp, void* mc, int world,
+                                                                int rank, size_t v0, size_t v1, float scale,
+                                                                uint32_t epoch, int want_sumsq) {
+  using V = PeerVec<DT>;
+  __shared__ float red[32];
+  start_barrier(pp, world, rank, epoch);
+  float ss = 0.f;
+  constexpr int U = 4;                               // switch round trips are long: keep four reductions in flight per thread
+  const size_t stride = (size_t)gridDim.x * blockDim.x;
+  for (size_t i0 = v0 + (size_t)blockIdx.x * blockDim.x + threadIdx.x; i0 < v1; i0 += stride * U) {
+    uint4 sum[U];
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const size_t i = i0 + (size_t)u * stride;
+      if (i < v1) sum[u] = McOps<DT>::ld_reduce(static_cast<const uint4*>(mc) + i);
+    }
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const size_t i = i0 + (size_t)u * stride;
+      if (i >= v1) break;
+      float x[8];
+      V::unpack(sum[u], x);
+#pragma unroll
+      for (int e = 0; e < 8; ++e) x[e] *= scale;
+      const uint4 out = V::pack(x);
+      if (want_sumsq) {
+        float y[8];
+        V::unpack(out, y);
+#pragma unroll
+        for (int e = 0; e < 8; ++e) ss = fmaf(y[e], y[e], ss);
+      }
+      if (SCATTER_ONLY) st_peer(static_cast<uint4*>(pp.buf[rank]) + i, out);
+      else McOps<DT>::st(static_cast<uint4*>(mc) + i, out);
+    }
+  }
+  if (want_sumsq) {
+    const float b = block_sum(ss, red);
+    if (threadIdx.x == 0) atomicAdd(reinterpret_cast<float*>(pp.flags[rank] + 32 + rank), b);
+  }
+  __shared__ bool last;
+  uint32_t* mine = pp.flags[rank];
+  __threadfence_system();
+  __syncthreads();
+  if (threadIdx.x == 0) last = (atomicAdd(mine + 16, 1u) == gridDim.x - 1);
+  __syncthreads();
+  if (!last) return;
+  __threadfence_system();
+  if ((int)threadIdx.x < world) {
+    if (want_sumsq && (int)threadIdx.x != rank) {
+      const uint32_t bits = ld_acquire_sys(mine + 32 + rank);
+      asm volatile("st.relaxed.sys.global.u32 [%0], %1;" :: "l"(pp.flags[threadIdx.x] + 32 + rank), "r"(bits) : "memory");
+      __threadfence_system();
+    }
+    st_release_sys(pp.flags[threadIdx.x] + 8 + rank, epoch);
+    wait_flag(mine + 8 + threadIdx.x, epoch, mine + 17);
+  }
+  if (threadIdx.x == 0) mine[16] = 0u;
+}
+
+}  // namespace
+
+extern "C" int b2_peer_allreduce_mc(void* mc_buf, void* const* peer_bufs, uint32_t* const* peer_flags, int world, int rank,
+                                    size_t offset_elems, size_t n, int dtype, float scale, unsigned epoch, int want_sumsq,
+                                    int scatter_only, int max_blocks, cudaStream_t stream) {
+  B2_REQUIRE(mc_buf, "b2_peer_allreduce_mc: null multicast pointer");
+  B2_REQUIRE(dtype == B2_F32 || dtype == B2_BF16, "b2_peer_allreduce_mc: dtype must be 0 (f32) or 1 (bf16)");
+  B2_REQUIRE(rank >= 0 && rank < world, "b2_peer_allreduce_mc: rank %d outside world %d", rank, world);
+  const size_t es = b2_dtype_size(dtype), per_vec = 16 / es;
+  B2_REQUIRE(n % per_vec == 0, "b2_peer_allreduce_mc: n (%zu) must be a multiple of %zu elements (16 bytes)", n, per_vec);
+  PeerPtrs pp;
+  int rc = fill_ptrs(pp, peer_bufs, peer_flags, world, offset_elems * es, "b2_peer_allreduce_mc");
+  if (rc != B2_OK) return rc;
+  void* mc = static_cast<char*>(mc_buf) + offset_elems * es;
+  B2_REQUIRE(b2_aligned(mc, 16), "b2_peer_allreduce_mc: multicast pointer (+offset) must be 16-byte aligned");
+  size_t v0, v1;
+  slice_of(n / per_vec, world, rank, v0, v1);
+  if (want_sumsq == 1) peer_zero_sumsq_kernel<<<1, 32, 0, stream>>>(pp.flags[rank]);
+  const unsigned grid = peer_grid(v1 - v0, max_blocks);
+  if (dtype == B2_BF16) {
+    if (scatter_only) peer_allreduce_mc_kernel<B2_BF16, true><<<grid, 512, 0, stream>>>(pp, mc, world, rank, v0, v1, scale, epoch, want_sumsq);
+    else peer_allreduce_mc_kernel<B2_BF16, false><<<grid, 512, 0, stream>>>(pp, mc, world, rank, v0, v1, scale, epoch, want_sumsq);
+  } else {
+    if (scatter_only) peer_allreduce_mc_kernel<B2_F32, true><<<grid, 512, 0, stream>>>(pp, mc, world, rank, v0, v1, scale, epoch, want_sumsq);
+    else peer_allreduce_mc_kernel<B2_F32, false><<<grid, 512, 0, stream>>>(pp, mc, world, rank, v0, v1, scale, epoch, want_sumsq);
+  }
+  B2_CHECK_CUDA(cudaGetLastError());
+  return B2_OK;
+}

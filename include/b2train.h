@@ -180,6 +180,13 @@ int b2_symm_free(void* dptr);
 int b2_peer_allreduce(void* const* peer_bufs, uint32_t* const* peer_flags, int world, int rank, size_t offset_elems,
                       size_t n, int dtype, float scale, unsigned epoch, int want_sumsq, int scatter_only,
                       int max_blocks, b2_stream_t stream);
+/* NVLS variant of b2_peer_allreduce: `mc_buf` is a multicast address aliasing the same offset of every rank's buffer
+ * (cuMulticast* / torch.distributed._symmetric_memory); the sum over ranks is formed inside the NVSwitch
+ * (multimem.ld_reduce, fp32 accumulation) and the result is broadcast with multimem.st. Same semantics and arguments
+ * otherwise; peer_bufs[rank] must still be the local mapping of the buffer. */
+int b2_peer_allreduce_mc(void* mc_buf, void* const* peer_bufs, uint32_t* const* peer_flags, int world, int rank,
+                         size_t offset_elems, size_t n, int dtype, float scale, unsigned epoch, int want_sumsq,
+                         int scatter_only, int max_blocks, b2_stream_t stream);
 int b2_peer_allgather(void* const* peer_bufs, uint32_t* const* peer_flags, int world, int rank, size_t offset_elems,
                       size_t n, int dtype, unsigned epoch, b2_stream_t stream);
 int b2_peer_slice(size_t n, int dtype, int world, int rank, size_t* begin, size_t* end);

@@ -46,6 +46,9 @@ def main():
             tol = 0 if (world == 2 or dtype == torch.float32) else float(want.float().abs().max()) * 2 ** -7
             if dtype == torch.float32 and world > 2:
                 tol = 1e-6                                    # different fp32 summation order than NCCL's ring
+            if comm.use_nvls and getattr(t._b2_symm[0], "mc_ptr", None):
+                # the NVSwitch forms the sum; its rounding of the bf16 result is within one ulp of ours
+                tol = max(tol, float(want.float().abs().max()) * 2 ** -7 if dtype == torch.bfloat16 else 1e-6)
             assert (t.float() - want.float()).abs().max() <= tol, (dtype, it, (t.float() - want.float()).abs().max())
             bits = t.view(torch.uint8).clone()
             b0 = bits.clone()
