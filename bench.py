@@ -15,6 +15,7 @@ Prints ONE JSON line (rank 0). `value` = tokens/s with the batch already residen
 driven through the public API from pinned host buffers, H2D copy and loss D2H inside the timed region.
 """
 import argparse
+import contextlib
 import json
 import os
 import subprocess
@@ -29,6 +30,13 @@ sys.path.insert(0, os.path.join(ROOT, "gke-ray-train_b200"))
 
 B_PER_GPU, SEQ, MAX_NORM, LR, WD = 8, 1024, 0.3, 2e-4, 1e-3
 METRIC = "train tokens/sec/box"
+# --workload: the default is the configuration BASELINE.json's metric is quoted on at N=1 (configs[1]); llama-1b is
+# configs[2] (Llama-3.2-1B shape, seq 2048, 2 sequences x 4 accumulation steps per GPU, ref: fine_tune_config.json:13-14)
+WORKLOADS = {
+    "gpt2-124m": dict(desc="gpt2-124m full fine-tune, seq 1024, bf16 (BASELINE configs[1])", b=8, t=1024, ga=1),
+    "llama-1b": dict(desc="llama-3.2-1b shape full fine-tune, seq 2048, bf16, 2 sequences x 4 accumulation steps per GPU "
+                          "(BASELINE configs[2])", b=2, t=2048, ga=4),
+}
 
 
 def load_peaks():
@@ -212,7 +220,10 @@ def run_ours(args):
     from oracle import torch_ref as TR       # model factory + synthetic data only (shared with the reference arm)
 
     peaks = load_peaks()
-    model = TR.make_gpt2(dtype=torch.bfloat16, seed=0)
+    global B_PER_GPU, SEQ
+    wl = WORKLOADS[args.workload]
+    B_PER_GPU, SEQ, GA = wl["b"], wl["t"], wl["ga"]
+    model = TR.make_gpt2(dtype=torch.bfloat16, seed=0) if args.workload == "gpt2-124m" else TR.make_llama(dtype=torch.bfloat16, seed=0)
     model.train()
     stock = args.impl == "stock-gpu"       # informational third arm: the reference's stock torch path on THIS GPU
     if stock:
@@ -231,14 +242,28 @@ def run_ours(args):
     V = inner.config.vocab_size
 
     n_batches = 4
-    host = [TR.synthetic_hf_batch(B_PER_GPU, SEQ, V, 1234 + 97 * rank + i) for i in range(n_batches)]
+    host = [TR.synthetic_hf_batch(B_PER_GPU * GA, SEQ, V, 1234 + 97 * rank + i) for i in range(n_batches)]
     pinned = [(a.pin_memory(), b.pin_memory()) for a, b in host]
     resident = [(a.to(device), b.to(device)) for a, b in host]
+    no_sync = getattr(model, "no_sync", None)
 
     def step(ids, labels):
         optimizer.zero_grad(set_to_none=True)
-        loss = model(input_ids=ids, labels=labels).loss
-        loss.backward()
+        if GA == 1:
+            loss = model(input_ids=ids, labels=labels).loss
+            loss.backward()
+        else:
+            # HF Trainer's accumulation: every micro-batch loss is sum-CE / (non-ignored labels of the whole step),
+            # gradient sync only on the last micro-batch ($SP/transformers/trainer.py:2109-2159; DDP.no_sync)
+            num_items = (labels[:, 1:] != -100).sum()
+            loss = 0.0
+            for k in range(GA):
+                sl = slice(k * B_PER_GPU, (k + 1) * B_PER_GPU)
+                ctx = no_sync() if (no_sync is not None and k < GA - 1) else contextlib.nullcontext()
+                with ctx:
+                    l = model(input_ids=ids[sl], labels=labels[sl], num_items_in_batch=num_items).loss
+                    l.backward()
+                loss = loss + l.detach()
         clip(model.parameters(), MAX_NORM)
         optimizer.step()
         return loss
@@ -279,7 +304,7 @@ def run_ours(args):
     ms_e2e, _, _ = timed(True)
     clocks = sampler.stop() if sampler else None      # sampled across both timed regions
 
-    tokens_per_step = world * B_PER_GPU * SEQ
+    tokens_per_step = world * B_PER_GPU * GA * SEQ
     value = tokens_per_step * args.steps / (ms_total * 1e-3)
     e2e = tokens_per_step * args.steps / (ms_e2e * 1e-3)
 
@@ -289,7 +314,7 @@ def run_ours(args):
         extra = [f3_roofline(torch, ops, device, peaks)]
     if world > 1:
         dist.barrier()
-    if rank == 0 and world == 1 and not args.no_cpu_baseline and not stock:
+    if rank == 0 and world == 1 and not args.no_cpu_baseline and not stock and args.workload == "gpt2-124m":
         torch.set_num_threads(os.cpu_count() or 1)
         r = TR.cpu_gpt2_baseline(steps=2, warmup=1, B=1, T=SEQ, dtype=torch.bfloat16)
         cpu = {"value": r["tokens_per_s"], "unit": "tokens/s", "cores": r["threads"], "kind": "port", "sample": r["sample"]}
@@ -299,13 +324,13 @@ def run_ours(args):
             "metric": METRIC, "value": value, "unit": "tokens/s", "n_gpus": world, "steps": args.steps,
             "warmup": max(args.warmup, 3), "ms_per_step": ms_total / args.steps, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
-            "config": {"workload": "gpt2-124m full fine-tune, seq 1024, bf16 (BASELINE configs[1])",
-                       "global_batch": world * B_PER_GPU, "seq_len": SEQ, "parallelism": f"dp{world}",
+            "config": {"workload": wl["desc"], "global_batch": world * B_PER_GPU * GA, "grad_accum": GA,
+                       "seq_len": SEQ, "parallelism": f"dp{world}",
                        "optimizer": "AdamW lr 2e-4 wd 1e-3, clip 0.3, pure-bf16 state",
                        "l2": "no explicit flush between steps: one step streams params+grads+AdamW state (1.0 GB) and >4 GB of "
                              "activations, far beyond the 126 MB L2; the roofline micro-runs flush 256 MB between iterations",
                        "last_loss": last_loss},
-            "e2e": {"value": e2e, "unit": "tokens/s", "h2d_bytes_per_step": 2 * B_PER_GPU * SEQ * 8, "d2h_bytes_per_step": 4,
+            "e2e": {"value": e2e, "unit": "tokens/s", "h2d_bytes_per_step": 2 * B_PER_GPU * GA * SEQ * 8, "d2h_bytes_per_step": 4,
                     "ms_per_step": ms_e2e / args.steps},
             "gpu_launches": launches, "clocks": clocks, "roofline": roof, "rooflines_other": extra, "cpu_baseline": cpu,
         }
@@ -324,6 +349,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference", "stock-gpu"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--workload", default="gpt2-124m", choices=sorted(WORKLOADS))
     args = ap.parse_args()
     if args.impl == "reference":
         return run_reference(args)
@@ -332,7 +358,7 @@ def main():
         # convenience: re-launch ourselves one rank per GPU
         cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={args.gpus}",
                "--master-addr", "127.0.0.1", "--master-port", "29517", os.path.abspath(__file__), "--gpus", str(args.gpus),
-               "--steps", str(args.steps), "--warmup", str(args.warmup), "--impl", args.impl] + (["--no-cpu-baseline"] if args.no_cpu_baseline else [])
+               "--steps", str(args.steps), "--warmup", str(args.warmup), "--impl", args.impl, "--workload", args.workload] + (["--no-cpu-baseline"] if args.no_cpu_baseline else [])
         raise SystemExit(subprocess.call(cmd))
     run_ours(args)
 
