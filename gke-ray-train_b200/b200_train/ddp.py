@@ -63,6 +63,10 @@ class DistributedDataParallel(nn.Module):
             dist.broadcast(buf.data, src=0, group=process_group)
             buf.comm = self.comm
             buf.reduced_sumsq = None
+            if self.shard_optimizer:
+                # ZeRO-1 style: rank r reduces, clips and updates only slice r of the flat buffer, then
+                # pushes its slice of the updated parameters to every peer; exp_avg / exp_avg_sq exist for that slice only
+                buf.shard_range = self.comm.slice_bounds(buf.numel, buf.dtype)
             buf._sumsq_store = torch.empty(self.world_size, dtype=torch.float32, device=device)
         for b in module.buffers():
             if b.is_cuda:
@@ -74,7 +78,7 @@ class DistributedDataParallel(nn.Module):
         # buckets are cut from the END of each buffer and launched in that fixed order on a side stream while the rest
         # of backward still runs.
         # (B2_DDP_OVERLAP / B2_DDP_BUCKET_MB / B2_DDP_MAX_BLOCKS override the arguments for measurements)
-        self.overlap = bool(int(os.environ.get("B2_DDP_OVERLAP", int(bool(overlap)))))
+        self.overlap = bool(int(os.environ.get("B2_DDP_OVERLAP", int(bool(overlap))))) and not self.shard_optimizer
         # measured on GPT-2 124M / 2 GPUs (profiles/README.md): 100 MiB buckets on <= 96 CTAs beat torch's 25 MiB default
         bucket_cap_mb = float(os.environ.get("B2_DDP_BUCKET_MB", 100 if bucket_cap_mb is None else bucket_cap_mb))
         self._overlap_blocks = int(os.environ.get("B2_DDP_MAX_BLOCKS", 96))
@@ -112,7 +116,8 @@ class DistributedDataParallel(nn.Module):
                 self.comm.allreduce_(b.buf.grad, want_sumsq=mode, offset=b.offset, numel=b.numel,
                                      max_blocks=0 if tail else self._overlap_blocks)      # nothing left to overlap with: whole GPU
         else:
-            self.comm.allreduce_(b.buf.grad, want_sumsq=mode, offset=b.offset, numel=b.numel)
+            self.comm.allreduce_(b.buf.grad, want_sumsq=mode, offset=b.offset, numel=b.numel,
+                                 scatter_only=self.shard_optimizer)
 
     def _launch_ready(self, force=False):
         while self._next_bucket < len(self._buckets):

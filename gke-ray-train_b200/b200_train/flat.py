@@ -10,6 +10,9 @@ prepare_model installs for the reference (ref: ray-jobs/pytorch_llm_ray.py:230).
 import torch
 
 ALIGN = 64  # elements; every parameter starts on a 64-element boundary (>= 128 B), padding stays zero
+# The buffer length is a multiple of 64 * lcm(1..8) elements, so that for any world size up to 8 the per-rank slices of
+# the peer-memory collectives (and of a sharded optimizer) are equal-sized and start on 64-element boundaries.
+TOTAL_MULTIPLE = 64 * 840
 
 
 class FlatBuffer:
@@ -23,7 +26,9 @@ class FlatBuffer:
         for p in self.params:
             self.offsets.append(off)
             off += (p.numel() + ALIGN - 1) // ALIGN * ALIGN
-        self.numel = off
+        self.numel = (off + TOTAL_MULTIPLE - 1) // TOTAL_MULTIPLE * TOTAL_MULTIPLE
+        self.shard_range = None      # (begin, end) when a data-parallel wrapper shards the optimizer over ranks
+        self.comm = None
         alloc = alloc or (lambda n, dt, dev: torch.zeros(n, dtype=dt, device=dev))
         self.data = alloc(self.numel, dtype, device)
         self.grad = alloc(self.numel, dtype, device)
@@ -68,7 +73,16 @@ class FlatBuffer:
 
 
 def flat_of(p):
-    return getattr(p, "_b2_flat", None)
+    """(FlatBuffer, offset) if `p` lives in a flat buffer. A deep-copied parameter carries a copy of the attribute but
+    not the storage, so the claim is verified against the buffer."""
+    f = getattr(p, "_b2_flat", None)
+    if f is None:
+        return None
+    buf, off = f
+    if p.data_ptr() != buf.data.data_ptr() + off * buf.data.element_size():
+        del p._b2_flat
+        return None
+    return f
 
 
 def flatten_params(params, alloc=None):

@@ -62,9 +62,10 @@ class AdamW(torch.optim.Optimizer):
         self._share_steps()
         for buf in self._buffers:
             sdt = self._state_dtype or buf.dtype      # torch: zeros_like(p) -> state dtype = param dtype
-            if buf.exp_avg is None:
-                buf.exp_avg = torch.zeros(buf.numel, dtype=sdt, device=buf.device)
-                buf.exp_avg_sq = torch.zeros(buf.numel, dtype=sdt, device=buf.device)
+            lo, hi = buf.shard_range or (0, buf.numel)
+            if buf.exp_avg is None:                   # sharded: state exists for this rank's slice only
+                buf.exp_avg = torch.zeros(hi - lo, dtype=sdt, device=buf.device)
+                buf.exp_avg_sq = torch.zeros(hi - lo, dtype=sdt, device=buf.device)
             table = torch.full((buf.numel // 64,), 255, dtype=torch.uint8)
             for p, o in zip(buf.params, buf.offsets):
                 if id(p) in gid:
@@ -75,9 +76,10 @@ class AdamW(torch.optim.Optimizer):
                 if id(p) not in gid:
                     continue
                 st = self.state[p]
-                # views into the flat state: state_dict() keeps torch's per-parameter layout
-                st["exp_avg"] = buf.exp_avg[o:o + p.numel()].view(p.shape)
-                st["exp_avg_sq"] = buf.exp_avg_sq[o:o + p.numel()].view(p.shape)
+                if buf.shard_range is None:
+                    # views into the flat state: state_dict() keeps torch's per-parameter layout
+                    st["exp_avg"] = buf.exp_avg[o:o + p.numel()].view(p.shape)
+                    st["exp_avg_sq"] = buf.exp_avg_sq[o:o + p.numel()].view(p.shape)
 
     def _share_steps(self):
         """All parameters of a group advance together, so they share one `step` tensor (saved per parameter by
@@ -129,10 +131,48 @@ class AdamW(torch.optim.Optimizer):
             hyper.append(dict(lr=g["lr"], beta1=b1, beta2=b2, eps=g["eps"], weight_decay=g["weight_decay"],
                               step=int(t.item())))
         for buf in self._buffers:
-            ops.adamw_grouped_(buf.data, buf.grad, buf.exp_avg, buf.exp_avg_sq, self._chunk_group[id(buf)], hyper,
-                               gscale=buf.pending_coef)
+            if buf.shard_range is None:
+                ops.adamw_grouped_(buf.data, buf.grad, buf.exp_avg, buf.exp_avg_sq, self._chunk_group[id(buf)], hyper,
+                                   gscale=buf.pending_coef)
+            else:
+                # this rank's slice only (its gradient slice is the one the reduce-scatter completed), then the updated
+                # slice is pushed to every peer's parameter buffer
+                lo, hi = buf.shard_range
+                ops.adamw_grouped_(buf.data[lo:hi], buf.grad[lo:hi], buf.exp_avg, buf.exp_avg_sq,
+                                   self._chunk_group[id(buf)][lo // 64:hi // 64], hyper, gscale=buf.pending_coef)
+                buf.comm.allgather_(buf.data)
             buf.pending_coef = None
         return loss
+
+    def _gathered_state(self, buf):
+        """Full-length exp_avg / exp_avg_sq of a sharded buffer (checkpoint path only; NCCL all-gather)."""
+        import torch.distributed as dist
+        full = []
+        for shard in (buf.exp_avg, buf.exp_avg_sq):
+            out = torch.empty(buf.numel, dtype=shard.dtype, device=shard.device)
+            dist.all_gather_into_tensor(out, shard.contiguous(), group=buf.comm.group)
+            full.append(out)
+        return full
+
+    def state_dict(self):
+        """torch's layout (`step`, `exp_avg`, `exp_avg_sq` per parameter, ref: pytorch_llm_ray.py:302) even when the
+        state is sharded over ranks: the shards are gathered for the occasion. Collective: call it on every rank."""
+        sharded = [b for b in (self._buffers or []) if b.shard_range is not None]
+        for buf in sharded:
+            m, v = self._gathered_state(buf)
+            for p, o in zip(buf.params, buf.offsets):
+                if p in self.state:
+                    self.state[p]["exp_avg"] = m[o:o + p.numel()].view(p.shape)
+                    self.state[p]["exp_avg_sq"] = v[o:o + p.numel()].view(p.shape)
+        sd = super().state_dict()
+        if sharded:
+            sd["state"] = {k: dict(v) for k, v in sd["state"].items()}      # detach from self.state before trimming it
+        for buf in sharded:
+            for p in buf.params:
+                if p in self.state:
+                    self.state[p].pop("exp_avg", None)
+                    self.state[p].pop("exp_avg_sq", None)
+        return sd
 
     def load_state_dict(self, state_dict):
         super().load_state_dict(state_dict)
@@ -140,13 +180,17 @@ class AdamW(torch.optim.Optimizer):
             return
         # re-home the loaded tensors into the flat state so the kernels see them
         for buf in self._buffers:
+            lo, hi = buf.shard_range or (0, buf.numel)
             for p, o in zip(buf.params, buf.offsets):
                 st = self.state.get(p)
-                if not st:
+                if not st or "exp_avg" not in st:
                     continue
                 for key, flat in (("exp_avg", buf.exp_avg), ("exp_avg_sq", buf.exp_avg_sq)):
-                    view = flat[o:o + p.numel()].view(p.shape)
-                    if st[key].data_ptr() != view.data_ptr():
-                        view.copy_(st[key])
-                        st[key] = view
+                    a, b = max(o, lo), min(o + p.numel(), hi)          # part of this parameter that lives in our state
+                    if a < b:
+                        flat[a - lo:b - lo].copy_(st[key].reshape(-1)[a - o:b - o])
+                    if buf.shard_range is None:
+                        st[key] = flat[o:o + p.numel()].view(p.shape)
+                    else:
+                        st.pop(key)
         self._share_steps()

@@ -63,27 +63,44 @@ def main():
         dist.barrier()
         assert (t.float() - want.float()).abs().max() <= tol
 
-    # --- prepare_model path on a tiny GPT-2
+    # --- prepare_model path on a tiny GPT-2: replicated optimizer (DDP semantics) and sharded optimizer (ZeRO-1 style)
     kw = dict(dtype=torch.bfloat16, seed=0, vocab_size=2003, n_embd=128, n_layer=2, n_head=4, n_positions=64,
               resid_pdrop=0.0, embd_pdrop=0.0, attn_pdrop=0.0)
-    torch.manual_seed(1000 + rank)                           # ranks start different; prepare_model syncs rank 0's weights
-    model = TR.make_gpt2(**{**kw, "seed": rank}).train()
-    b200.patch_causal_lm(model)
-    model = b200.prepare_model(model)
-    assert hasattr(model, "module")
-    opt = b200.AdamW(TR.hf_param_groups(model.module, 1e-3), lr=2e-4)
     batches = [TR.synthetic_hf_batch(4, 64, 2003, seed=50 + r, device=dev) for r in range(world)]
-    for step in range(2):
-        opt.zero_grad(set_to_none=True)
-        ids, lab = batches[rank]
-        loss = model(input_ids=ids, labels=lab).loss
-        loss.backward()
-        norm = b200.clip_grad_norm_(model.parameters(), 0.3)
-        opt.step()
-    flat = torch.cat([p.detach().float().reshape(-1) for p in model.parameters()])
-    f0 = flat.clone()
-    dist.broadcast(f0, 0)
-    assert torch.equal(flat, f0), "parameters diverged across ranks"
+
+    def run_ddp(shard):
+        torch.manual_seed(1000 + rank)                       # ranks start different; prepare_model syncs rank 0's weights
+        model = TR.make_gpt2(**{**kw, "seed": rank}).train()
+        b200.patch_causal_lm(model)
+        model = b200.prepare_model(model, parallel_strategy_kwargs={"shard_optimizer": shard})
+        assert hasattr(model, "module")
+        opt = b200.AdamW(TR.hf_param_groups(model.module, 1e-3), lr=2e-4)
+        for step in range(2):
+            opt.zero_grad(set_to_none=True)
+            ids, lab = batches[rank]
+            loss = model(input_ids=ids, labels=lab).loss
+            loss.backward()
+            b200.clip_grad_norm_(model.parameters(), 0.3)
+            opt.step()
+        flat = torch.cat([p.detach().float().reshape(-1) for p in model.parameters()])
+        f0 = flat.clone()
+        dist.broadcast(f0, 0)
+        assert torch.equal(flat, f0), "parameters diverged across ranks"
+        sd = opt.state_dict()                                # collective when sharded
+        return model, opt, flat, sd
+
+    model, opt, flat, sd = run_ddp(False)
+    model_s, opt_s, flat_s, sd_s = run_ddp(True)
+    assert torch.equal(flat, flat_s), "sharded optimizer must give bit-identical parameters"
+    assert sd["state"].keys() == sd_s["state"].keys()
+    for k in sd["state"]:
+        assert float(sd["state"][k]["step"]) == float(sd_s["state"][k]["step"]) == 2.0
+        assert torch.equal(sd["state"][k]["exp_avg"], sd_s["state"][k]["exp_avg"]), k
+        assert torch.equal(sd["state"][k]["exp_avg_sq"], sd_s["state"][k]["exp_avg_sq"]), k
+    # optimizer memory is really sharded
+    full = sum(b.numel for b in opt.flat_buffers()); part = sum(b.exp_avg.numel() for b in opt_s.flat_buffers())
+    assert part * world == full, (part, full)
+    model_s.close()
     # stock single-process equivalent: DDP averages per-rank mean losses -> emulate by averaging gradients
     ref = TR.make_gpt2(**kw).to(dev).train()
     ropt = torch.optim.AdamW(TR.hf_param_groups(ref, 1e-3), lr=2e-4)

@@ -300,3 +300,35 @@ def test_peer_allreduce_single_gpu_emulation(b200):
         torch.cuda.synchronize()
         for b in bufs2:
             assert torch.equal(b, bufs[0])
+
+
+# ------------------------------------------------------------------------------------------ checkpoint parity (§8f-1)
+def test_optimizer_state_dict_roundtrip_matches_torch(b200):
+    """optimizer.state_dict() (ref: pytorch_llm_ray.py:302) is interchangeable with torch.optim.AdamW's: a checkpoint
+    written by torch resumes in ours (and vice versa) and the next step lands on the same parameters."""
+    torch.manual_seed(0)
+    m_ref = nn.Sequential(nn.Linear(64, 128), nn.GELU(), nn.Linear(128, 32)).to(dev())
+    m_my = copy.deepcopy(m_ref)
+    o_ref = torch.optim.AdamW(m_ref.parameters(), lr=1e-3, weight_decay=0.01)
+    o_my = b200.AdamW(m_my.parameters(), lr=1e-3, weight_decay=0.01)
+    x = torch.randn(16, 64, device=dev())
+    for _ in range(2):
+        for m, o in ((m_ref, o_ref), (m_my, o_my)):
+            o.zero_grad(set_to_none=True)
+            m(x).pow(2).mean().backward()
+            o.step()
+    # torch -> ours
+    m_a = copy.deepcopy(m_ref); o_a = b200.AdamW(m_a.parameters(), lr=1e-3, weight_decay=0.01)
+    o_a.load_state_dict(copy.deepcopy(o_ref.state_dict()))
+    # ours -> torch
+    m_b = copy.deepcopy(m_my); o_b = torch.optim.AdamW(m_b.parameters(), lr=1e-3, weight_decay=0.01)
+    o_b.load_state_dict(copy.deepcopy(o_my.state_dict()))     # state_dict() hands out live tensors, as torch's does
+    for m, o in ((m_ref, o_ref), (m_a, o_a), (m_my, o_my), (m_b, o_b)):
+        o.zero_grad(set_to_none=True)
+        m(x).pow(2).mean().backward()
+        o.step()
+    for pr, pa in zip(m_ref.parameters(), m_a.parameters()):
+        np.testing.assert_allclose(pa.detach().cpu().numpy(), pr.detach().cpu().numpy(), rtol=0, atol=1e-7)
+    for pm, pb in zip(m_my.parameters(), m_b.parameters()):
+        np.testing.assert_allclose(pb.detach().cpu().numpy(), pm.detach().cpu().numpy(), rtol=0, atol=1e-7)
+    assert float(o_a.state_dict()["state"][0]["step"]) == 3.0
