@@ -15,3 +15,4 @@ from .optim import AdamW  # noqa: E402,F401
 from . import train  # noqa: E402,F401
 from .train import (Checkpoint, CheckpointConfig, Result, RunConfig, ScalingConfig, TorchConfig,  # noqa: E402,F401
                     TorchTrainer)
+from .data import ResidentWindowLoader  # noqa: E402,F401

@@ -147,6 +147,14 @@ int b2_gemm_bf16(const void* A, int a_mn_major, long long lda, const void* B, in
  * range is split up to 6 ways into fp32 partials that a second kernel adds in a fixed order. NULL = never split. */
 size_t b2_gemm_workspace_bytes(int M, int N);
 
+/* ---- input side: sliding token windows gathered on the device -------------------------------------------------
+ * Replaces TextDataset.__getitem__ + DataLoader collate + the host-to-device copy of prepare_data_loader — ref:
+ * ray-jobs/pytorch_llm_ray.py:107-119, 206-216. tokens: int64 [n_tokens] resident on the device; starts: int64 [B];
+ * inputs[b,t] = tokens[starts[b]+t], targets[b,t] = tokens[starts[b]+t+1] (int64 [B,T] each). A window that does not
+ * fit (start < 0 or start + T + 1 > n_tokens) sets err_out[0] = 1 (nullable) and yields zeros. */
+int b2_gather_windows(const long long* tokens, long long n_tokens, const long long* starts, int B, int T,
+                      long long* inputs, long long* targets, int* err_out, b2_stream_t stream);
+
 /* ---- F2: gradient all-reduce over peer memory (NVLink 5 / NVSwitch) ----------------------------------
  * Replaces the bucket all-reduce (+ the grad / world_size copy-in) that DistributedDataParallel performs during
  * loss.backward() once ray.train.torch.prepare_model has wrapped the model — ref: ray-jobs/pytorch_llm_ray.py:230,276;

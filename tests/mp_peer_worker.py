@@ -101,6 +101,31 @@ def main():
     full = sum(b.numel for b in opt.flat_buffers()); part = sum(b.exp_avg.numel() for b in opt_s.flat_buffers())
     assert part * world == full, (part, full)
     model_s.close()
+    # --- gradient accumulation: two micro-batches, the first under no_sync() (ref: fine_tune_config.json:14)
+    torch.manual_seed(7)
+    acc_model = b200.prepare_model(b200.patch_causal_lm(TR.make_gpt2(**kw).train()))
+    acc_opt = b200.AdamW(TR.hf_param_groups(acc_model.module, 1e-3), lr=2e-4)
+    mb = [TR.synthetic_hf_batch(2, 64, 2003, seed=900 + 10 * rank + k, device=dev) for k in range(2)]
+    n_items = sum(int((lab[:, 1:] != -100).sum()) for _, lab in mb)
+    acc_opt.zero_grad(set_to_none=True)
+    with acc_model.no_sync():
+        acc_model(input_ids=mb[0][0], labels=mb[0][1], num_items_in_batch=n_items).loss.backward()
+    g_before = acc_model.buffers[0].grad.clone()
+    acc_model(input_ids=mb[1][0], labels=mb[1][1], num_items_in_batch=n_items).loss.backward()
+    # after the synchronised backward every rank holds the same averaged gradient; it differs from the local partial one
+    g = acc_model.buffers[0].grad.clone()
+    g0 = g.clone(); dist.broadcast(g0, 0)
+    assert torch.equal(g, g0) and not torch.equal(g, g_before)
+    # and equals the mean over ranks of the locally accumulated gradients, computed the slow way
+    chk = b200.patch_causal_lm(TR.make_gpt2(**kw).to(dev).train())
+    for ids, lab in mb:
+        chk(input_ids=ids, labels=lab, num_items_in_batch=n_items).loss.backward()
+    local = torch.cat([p.grad.reshape(-1).float() for p in chk.parameters()])
+    dist.all_reduce(local); local /= world
+    got = torch.cat([p.grad.reshape(-1).float() for p in acc_model.module.parameters()])
+    assert (got - local).abs().max() <= 2.0 ** -7 * local.abs().max() + 1e-6
+    acc_model.close()
+
     # stock single-process equivalent: DDP averages per-rank mean losses -> emulate by averaging gradients
     ref = TR.make_gpt2(**kw).to(dev).train()
     ropt = torch.optim.AdamW(TR.hf_param_groups(ref, 1e-3), lr=2e-4)

@@ -332,3 +332,27 @@ def test_optimizer_state_dict_roundtrip_matches_torch(b200):
     for pm, pb in zip(m_my.parameters(), m_b.parameters()):
         np.testing.assert_allclose(pb.detach().cpu().numpy(), pm.detach().cpu().numpy(), rtol=0, atol=1e-7)
     assert float(o_a.state_dict()["state"][0]["step"]) == 3.0
+
+
+# ------------------------------------------------------------------------------------------ input side (§8f-3)
+def test_resident_window_loader_matches_reference_pipeline(b200):
+    """Batch for batch identical (integers: bit-exact) to TextDataset -> Subset -> DataLoader(shuffle, drop_last) ->
+    prepare_data_loader's DistributedSampler, for both ranks of a 2-worker job."""
+    from torch.utils.data import DataLoader, DistributedSampler, Subset, TensorDataset
+    stream = TR.synthetic_char_stream(5000, 283)
+    T, B, limit = 64, 16, 1000
+    for rank in (0, 1):
+        n = min(max(0, len(stream) - T - 1), limit)
+        xs, ys = TR.windows(stream, torch.arange(n), T)                 # == TextDataset[i] (pinned by make_golden.py)
+        ds = TensorDataset(xs, ys)
+        sampler = DistributedSampler(ds, num_replicas=2, rank=rank, shuffle=True, seed=0)
+        ref = DataLoader(ds, batch_size=B, sampler=sampler, drop_last=True)
+        mine = b200.ResidentWindowLoader(stream, T, B, dev(), shuffle=True, num_replicas=2, rank=rank, limit=limit)
+        for epoch in (0, 1):
+            sampler.set_epoch(epoch); mine.sampler.set_epoch(epoch)
+            assert len(mine) == len(ref)
+            for (rx, ry), (mx, my) in zip(ref, mine):
+                assert torch.equal(mx.cpu(), rx) and torch.equal(my.cpu(), ry)
+    # a window that does not fit is flagged, not read out of bounds
+    bad = mine.gather(torch.tensor([len(stream) - T], device=dev()))
+    assert int(mine._err.item()) == 1 and int(bad[0].abs().sum()) == 0

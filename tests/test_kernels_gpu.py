@@ -78,7 +78,8 @@ def make_labels(rng, N, V, frac_ignored=0.2):
     return y
 
 
-@pytest.mark.parametrize("N,D,V", [(128, 64, 256), (384, 192, 1000), (200, 256, 283), (1024, 768, 5003)])
+@pytest.mark.parametrize("N,D,V", [(128, 64, 256), (384, 192, 1000), (200, 256, 283), (1024, 768, 5003),
+                                   (8, 72, 8), (136, 1032, 257), (264, 64, 40)])     # ragged in every dimension
 @pytest.mark.parametrize("shift_T", [0, 8])
 @pytest.mark.parametrize("with_bias", [False, True])
 def test_lmhead_ce_fwd_matches_oracle(ops, N, D, V, shift_T, with_bias):
@@ -105,6 +106,18 @@ def test_lmhead_ce_fwd_matches_oracle(ops, N, D, V, shift_T, with_bias):
     np.testing.assert_allclose(r2.lse[:N].cpu().numpy(), o2["lse"], rtol=0, atol=4e-2)
     if o2["n_valid"]:
         np.testing.assert_allclose(r2.loss_mean.item(), o2["loss"], rtol=0, atol=2e-3)
+
+
+def test_lmhead_ce_rejects_unaligned_shapes(ops):
+    """TMA needs 16-byte-aligned rows: a hidden size that is not a multiple of 8 is an error, never a silent fallback."""
+    from b200_train import B2Error
+    H = torch.zeros(16, 100, dtype=torch.bfloat16, device=dev())[:, :99]
+    W = torch.zeros(32, 100, dtype=torch.bfloat16, device=dev())[:, :99]
+    y = torch.zeros(16, dtype=torch.int64, device=dev())
+    with pytest.raises(B2Error):
+        ops.lmhead_ce_fwd(H.contiguous(), W.contiguous(), y)
+    with pytest.raises(B2Error):
+        ops.lmhead_ce_fwd(torch.zeros(16, 64, device=dev()), torch.zeros(32, 64, device=dev()), y)     # fp32 inputs
 
 
 def test_lmhead_ce_edge_cases(ops):
