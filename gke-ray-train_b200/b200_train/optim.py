@@ -165,8 +165,13 @@ class AdamW(torch.optim.Optimizer):
                     self.state[p]["exp_avg"] = m[o:o + p.numel()].view(p.shape)
                     self.state[p]["exp_avg_sq"] = v[o:o + p.numel()].view(p.shape)
         sd = super().state_dict()
-        if sharded:
-            sd["state"] = {k: dict(v) for k, v in sd["state"].items()}      # detach from self.state before trimming it
+        # Detach the per-parameter dicts from self.state, and give every parameter its OWN step tensor: internally one
+        # tensor per group is shared, but torch's optimizers increment each entry they are handed (foreach), so a
+        # checkpoint carrying a shared tensor would advance several steps at once after being loaded there.
+        sd["state"] = {k: dict(v) for k, v in sd["state"].items()}
+        for v in sd["state"].values():
+            if isinstance(v.get("step"), torch.Tensor):
+                v["step"] = v["step"].clone()
         for buf in sharded:
             for p in buf.params:
                 if p in self.state:
