@@ -162,6 +162,12 @@ class DistributedDataParallel(nn.Module):
 
     # ------------------------------------------------------------------ nn.Module surface
     def forward(self, *args, **kwargs):
+        self.forward_prepare()
+        return self.module(*args, **kwargs)
+
+    def forward_prepare(self):
+        """Forward-side bookkeeping (gradient views in place, stale reductions forgotten). forward() calls it; call it
+        yourself only when you drive `self.module` piecewise (e.g. its feature extractor + a fused loss)."""
         for buf in self.buffers:
             missing = [i for i, p in enumerate(buf.params) if p.grad is None]
             if missing:
@@ -174,7 +180,6 @@ class DistributedDataParallel(nn.Module):
                         buf.grad_view(i).zero_()
                 buf.install_grads()
             buf.reduced_sumsq = None
-        return self.module(*args, **kwargs)
 
     @contextlib.contextmanager
     def no_sync(self):
