@@ -216,8 +216,8 @@ def run_ours(args):
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         dist.init_process_group("nccl", device_id=device)
     import b200_train as b200
+    import workloads as TR                   # model factories + synthetic inputs, shared with the reference arm
     from b200_train import _lib, ops
-    from oracle import torch_ref as TR       # model factory + synthetic data only (shared with the reference arm)
 
     peaks = load_peaks()
     global B_PER_GPU, SEQ
@@ -315,8 +315,10 @@ def run_ours(args):
     if world > 1:
         dist.barrier()
     if rank == 0 and world == 1 and not args.no_cpu_baseline and not stock and args.workload == "gpt2-124m":
+        # the one place this arm touches oracle/: the reported CPU baseline (the reference's stock call sequence)
+        from oracle import torch_ref as REF
         torch.set_num_threads(os.cpu_count() or 1)
-        r = TR.cpu_gpt2_baseline(steps=2, warmup=1, B=1, T=SEQ, dtype=torch.bfloat16)
+        r = REF.cpu_gpt2_baseline(steps=2, warmup=1, B=1, T=SEQ, dtype=torch.bfloat16)
         cpu = {"value": r["tokens_per_s"], "unit": "tokens/s", "cores": r["threads"], "kind": "port", "sample": r["sample"]}
     if rank == 0:
         line = {

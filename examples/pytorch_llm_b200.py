@@ -26,7 +26,7 @@ sys.path.insert(0, os.path.join(ROOT, "gke-ray-train_b200"))
 def train_loop_per_worker(config):
     import b200_train
     from b200_train import train
-    from oracle import torch_ref as TR          # model definition + synthetic data only
+    import workloads as TR                       # model definition + synthetic data
 
     session = train.get_context()
     world_rank, world_size = session.get_world_rank(), session.get_world_size()
