@@ -87,16 +87,25 @@ struct Unit { int mb, s, ks, nb0, nb1, kb0, kb1; };
 // Work unit u -> (128-row block, vocabulary/column range, K range). Units that are adjacent in u run at the same
 // time on neighbouring CTAs, so the fastest-varying coordinate decides which operand tile they share through L2.
 __device__ __forceinline__ Unit decode_unit(const Params& p, int u) {
+  // 32-bit unsigned arithmetic throughout (all counts are far below 2^31): this runs on the single TMA and MMA threads
+  // at every unit boundary, where a chain of 64-bit divisions would leave the tensor pipe idle.
   Unit t;
-  const int per_k = p.num_m_blocks * p.n_splits;
-  t.ks = u / per_k;
-  const int r = u - t.ks * per_k;
-  if (p.n_fastest) { t.mb = r / p.n_splits; t.s = r - t.mb * p.n_splits; }
-  else { t.s = r / p.num_m_blocks; t.mb = r - t.s * p.num_m_blocks; }
-  t.nb0 = (int)((long long)t.s * p.num_n_blocks / p.n_splits);
-  t.nb1 = (int)((long long)(t.s + 1) * p.num_n_blocks / p.n_splits);
-  t.kb0 = (int)((long long)t.ks * p.num_k_blocks / p.k_splits);
-  t.kb1 = (int)((long long)(t.ks + 1) * p.num_k_blocks / p.k_splits);
+  const uint32_t per_k = (uint32_t)(p.num_m_blocks * p.n_splits), uu = (uint32_t)u;
+  const uint32_t ks = uu / per_k, r = uu - ks * per_k;
+  uint32_t mb, s;
+  if (p.n_fastest) { mb = r / (uint32_t)p.n_splits; s = r - mb * (uint32_t)p.n_splits; }
+  else { s = r / (uint32_t)p.num_m_blocks; mb = r - s * (uint32_t)p.num_m_blocks; }
+  t.ks = (int)ks; t.mb = (int)mb; t.s = (int)s;
+  if (p.n_splits == p.num_n_blocks) { t.nb0 = (int)s; t.nb1 = (int)s + 1; }
+  else {
+    t.nb0 = (int)(s * (uint32_t)p.num_n_blocks / (uint32_t)p.n_splits);
+    t.nb1 = (int)((s + 1) * (uint32_t)p.num_n_blocks / (uint32_t)p.n_splits);
+  }
+  if (p.k_splits == 1) { t.kb0 = 0; t.kb1 = p.num_k_blocks; }
+  else {
+    t.kb0 = (int)(ks * (uint32_t)p.num_k_blocks / (uint32_t)p.k_splits);
+    t.kb1 = (int)((ks + 1) * (uint32_t)p.num_k_blocks / (uint32_t)p.k_splits);
+  }
   return t;
 }
 
@@ -174,6 +183,9 @@ umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
       constexpr uint32_t idesc = make_idesc_bf16(BM * NC, BN, A_MN, B_MN);
       int stage = 0; uint32_t phase = 0;
       int as = 0; uint32_t aphase = 0;
+      const uint32_t a_addr0 = smem_u32(smem), b_addr0 = a_addr0 + A_STAGE_BYTES;
+      const uint64_t adesc0 = A_MN ? make_sdesc_sw128(a_addr0, BOX_MN_BYTES, 1024) : make_sdesc_sw128(a_addr0, 16, 1024);
+      const uint64_t bdesc0 = B_MN ? make_sdesc_sw128(b_addr0, BOX_MN_BYTES, 1024) : make_sdesc_sw128(b_addr0, 16, 1024);
       for (int u = cid; u < num_units; u += ncl) {
         const Unit t = decode_unit(p, u);
         for (int nb = t.nb0; nb < t.nb1; ++nb) {
@@ -183,14 +195,13 @@ umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
           for (int kb = t.kb0; kb < t.kb1; ++kb) {
             mbar_wait(&full_bar[stage], phase);
             tc_fence_after();
-            const uint32_t a_addr = smem_u32(smem + stage * STAGE_BYTES);
-            const uint32_t b_addr = a_addr + A_STAGE_BYTES;
+            // descriptors differ from the stage-0 / k-0 ones only in the 14-bit start-address field (16-byte units)
+            const uint64_t adesc_s = adesc0 + (uint64_t)((uint32_t)(stage * STAGE_BYTES) >> 4);
+            const uint64_t bdesc_s = bdesc0 + (uint64_t)((uint32_t)(stage * STAGE_BYTES) >> 4);
 #pragma unroll
             for (int k = 0; k < BK / UK; ++k) {
-              const uint64_t adesc = A_MN ? make_sdesc_sw128(a_addr + k * (UK * 128), BOX_MN_BYTES, 1024)
-                                          : make_sdesc_sw128(a_addr + k * (UK * 2), 16, 1024);
-              const uint64_t bdesc = B_MN ? make_sdesc_sw128(b_addr + k * (UK * 128), BOX_MN_BYTES, 1024)
-                                          : make_sdesc_sw128(b_addr + k * (UK * 2), 16, 1024);
+              const uint64_t adesc = adesc_s + (uint64_t)((A_MN ? k * (UK * 128) : k * (UK * 2)) >> 4);
+              const uint64_t bdesc = bdesc_s + (uint64_t)((B_MN ? k * (UK * 128) : k * (UK * 2)) >> 4);
               if (PAIR) mma_bf16_ss_pair(tmem_d, adesc, bdesc, idesc, (uint32_t)(kb > t.kb0 || k > 0));
               else mma_bf16_ss(tmem_d, adesc, bdesc, idesc, (uint32_t)(kb > t.kb0 || k > 0));
             }
@@ -252,6 +263,7 @@ umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
             if (gt == 0) bulk_wait_read_1();         // the store issued two boxes ago has drained its buffer
             named_bar_sync(1 + half, 128);
           }
+          if (MODE == MODE_GEMM && p.c_dtype == 98) continue;   // measurement aid (B2_DEBUG_NOEPI=2): not even the TMEM read
           uint32_t r[32];
           tmem_ld_32x32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(as * BN + c * 32), r);
           tmem_ld_wait();
@@ -619,8 +631,9 @@ extern "C" int b2_gemm_bf16(const void* A, int a_mn_major, long long lda, const 
     p.k_splits = auto_k_splits(p.num_m_blocks * p.num_n_blocks, p.num_k_blocks, num_workers(MODE_GEMM));
   p.ws = static_cast<float*>(workspace); p.ldws = ((long long)N + 3) / 4 * 4;
   p.C = C; p.ldc = ldc; p.c_dtype = c_dtype; p.accumulate = accumulate;
-  static const bool noepi = getenv("B2_DEBUG_NOEPI") != nullptr;     // profiling only: mainloop ceiling without stores
-  if (noepi) { p.c_dtype = 99; p.k_splits = 1; }
+  // profiling only: mainloop ceiling without the epilogue stores (=1) or without even reading the accumulator (=2)
+  static const int noepi = [] { const char* e = getenv("B2_DEBUG_NOEPI"); return e == nullptr ? 0 : (e[0] == '2' ? 2 : 1); }();
+  if (noepi) { p.c_dtype = noepi == 2 ? 98 : 99; p.k_splits = 1; }
   if (!a_mn_major && !b_mn_major) rc = launch<MODE_GEMM, 0, 0>(ta, tb, ta, p, stream);
   else if (!a_mn_major && b_mn_major) rc = launch<MODE_GEMM, 0, 1>(ta, tb, ta, p, stream);
   else if (a_mn_major && !b_mn_major) rc = launch<MODE_GEMM, 1, 0>(ta, tb, ta, p, stream);
