@@ -506,13 +506,14 @@ int num_sms() {
   return n;
 }
 
-// CTA pairs (tcgen05 cta_group::2, M = 256 per MMA) for the forward and the plain GEMMs; the dlogits kernel, whose
-// epilogue is the heavier side, measured faster with independent CTAs (profiles/). B2_PAIR=0 / B2_PAIR=1 in the
-// environment forces one shape everywhere (A/B measurements).
+// CTA pairs (tcgen05 cta_group::2, M = 256 per MMA) for the plain GEMMs (long K, light epilogue); the two cross-entropy
+// kernels, whose epilogues are the heavier side, measured faster with independent CTAs that are not coupled through a
+// shared accumulator hand-off (profiles/README.md). B2_PAIR=0 / B2_PAIR=1 in the environment forces one shape
+// everywhere (A/B measurements).
 bool use_pair(int mode) {
   static const int forced = [] { const char* e = getenv("B2_PAIR"); return e == nullptr ? -1 : (e[0] != '0'); }();
   if (forced >= 0) return forced != 0;
-  return mode != MODE_CE_BWD;
+  return mode == MODE_GEMM;
 }
 // rows of A covered by one work unit
 int rows_per_unit(int mode) { return use_pair(mode) ? 2 * BM : BM; }
