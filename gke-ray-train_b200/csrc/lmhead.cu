@@ -45,7 +45,7 @@ constexpr int A_STAGE_BYTES = BM * BK * 2;            // 16 KiB: this CTA's 128 
 constexpr int b_stage_bytes(bool pair) { return (pair ? BN / 2 : BN) * BK * 2; }
 constexpr int stage_bytes(bool pair) { return A_STAGE_BYTES + b_stage_bytes(pair); }
 constexpr int stages_for(bool pair) { return pair ? 6 : 4; }                 // 192 KiB of operand ring either way
-constexpr int STAGING_BYTES = 4 * BM * 64;           // MODE_CE_BWD: 2 column halves x 2 alternating [128 rows x 64 B] boxes
+constexpr int STAGING_BYTES = 8 * 2 * 32 * 64;        // MODE_CE_BWD: 8 epilogue warps x 2 alternating [32 rows x 64 B] blocks
 constexpr int smem_bytes_for(int mode, bool pair) {  // + 1 KiB slack to reach 1024-byte alignment
   return stages_for(pair) * stage_bytes(pair) + 1024 + (mode == 2 ? STAGING_BYTES : 0);
 }
@@ -222,9 +222,9 @@ umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
     const int q = warp & 3;
     const int half = (warp - 4) >> 2;               // 0: tile columns [0,128)   1: [128,256)
     const int trow = q * 32 + lane;                 // row inside the tile
-    const int gt = (int)threadIdx.x - 128 - half * 128;   // thread index inside this column-half group (0..127)
     int as = 0; uint32_t aphase = 0;
     uint32_t store_seq = 0;                         // MODE_CE_BWD: staging box toggle
+    const uint64_t store_policy = l2_policy_evict_first();
     for (int u = cid; u < num_units; u += ncl) {
       const Unit t = decode_unit(p, u);
       const int s = t.s, nb0 = t.nb0, nb1 = t.nb1;
@@ -236,13 +236,13 @@ umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
       float run_m = -INFINITY, run_s = 0.f, zval = 0.f;
       bool z_found = false;
       long long y = -1;
-      float row_lse_l2 = 0.f, gs = 0.f;
+      float gs = 0.f, bwd_off = -INFINITY;
       if (MODE != MODE_GEMM && row_ok) {
         y = label_at(p, p.row0 + row);
         if (MODE == MODE_CE_BWD) {
           const bool valid = (y != p.ignore_index) && y >= 0 && y < p.N;
-          row_lse_l2 = p.lse[p.row0 + row] * LOG2E;
           gs = valid ? __ldg(p.gscale) : 0.f;
+          if (gs != 0.f) bwd_off = log2f(fabsf(gs)) - p.lse[p.row0 + row] * LOG2E;
           if (!valid) y = -1;
         }
       }
@@ -256,12 +256,12 @@ umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
           const int col0 = nb * BN + c * 32;
           if (MODE != MODE_CE_BWD && col0 >= p.N) break;   // warp-uniform: nothing but padding from here on
           if (MODE == MODE_CE_BWD) {
-            // d(logits) leaves through shared memory: each 32-column chunk fills one [128 rows x 64 B] box in the
-            // 64B-swizzled layout, which one thread hands to the TMA engine (coalesced store, clipped at the matrix
-            // edge by the tensor map). Each column-half group owns two boxes and alternates between them.
-            if (col0 >= p.N) break;                  // group-uniform: box entirely beyond the vocabulary
-            if (gt == 0) bulk_wait_read_1();         // the store issued two boxes ago has drained its buffer
-            named_bar_sync(1 + half, 128);
+            // d(logits) leaves through shared memory: each warp stages its own [32 rows x 32 columns] bf16 block (2 KiB,
+            // 64B-swizzled) and one lane hands it to the TMA engine (coalesced store, clipped at the matrix edge by the
+            // tensor map). Two blocks per warp alternate; nothing here synchronises across warps.
+            if (col0 >= p.N) break;                  // warp-uniform: block entirely beyond the vocabulary
+            if (lane == 0) bulk_wait_read_1();       // the store issued two blocks ago has drained its buffer
+            __syncwarp();
           }
           if (MODE == MODE_GEMM && p.c_dtype == 98) continue;   // measurement aid (B2_DEBUG_NOEPI=2): not even the TMEM read
           uint32_t r[32];
@@ -361,23 +361,33 @@ umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
                 z_found = true;
               }
             } else {  // MODE_CE_BWD
-              const int jj = (y >= col0 && y < col0 + 32) ? (int)(y - col0) : -1;
+              // softmax * gscale in one FFMA + EX2 per element: the scale rides in the exponent offset
+              // (bwd_off = log2|gscale| - lse*log2e; -inf for ignored rows, which therefore come out as exact zeros)
+              float d[32];
+#pragma unroll
+              for (int j = 0; j < 32; ++j) d[j] = fast_exp2(fmaf(x[j], LOG2E, bwd_off));
+              if (y >= col0 && y < col0 + 32) {      // the label's column: subtract the one-hot term (once per row)
+                const int jj = (int)(y - col0);
+#pragma unroll
+                for (int j = 0; j < 32; ++j) if (j == jj) d[j] -= fabsf(gs);
+              }
+              if (gs < 0.f) {                         // uniform: a negative upstream gradient flips every sign
+#pragma unroll
+                for (int j = 0; j < 32; ++j) d[j] = -d[j];
+              }
               uint32_t w[16];
 #pragma unroll
-              for (int j = 0; j < 32; j += 2) {
-                const float p0 = fast_exp2(fmaf(x[j], LOG2E, -row_lse_l2));
-                const float p1 = fast_exp2(fmaf(x[j + 1], LOG2E, -row_lse_l2));
-                w[j >> 1] = pack_bf16((p0 - (j == jj ? 1.f : 0.f)) * gs, (p1 - (j + 1 == jj ? 1.f : 0.f)) * gs);
-              }
-              uint8_t* box = smem + STAGES * STAGE_BYTES + (half * 2 + (int)(store_seq & 1)) * (BM * 64);
-              uint8_t* rowp = box + trow * 64;
+              for (int j = 0; j < 32; j += 2) w[j >> 1] = pack_bf16(d[j], d[j + 1]);
+              uint8_t* box = smem + STAGES * STAGE_BYTES + ((warp - 4) * 2 + (int)(store_seq & 1)) * (32 * 64);
+              uint8_t* rowp = box + lane * 64;
 #pragma unroll
               for (int k = 0; k < 4; ++k)             // 16-byte chunk k of the 64-byte row, SWIZZLE_64B: k ^ ((row >> 1) & 3)
-                st_shared_v4(rowp + ((k ^ ((trow >> 1) & 3)) << 4), w[4 * k], w[4 * k + 1], w[4 * k + 2], w[4 * k + 3]);
+                st_shared_v4(rowp + ((k ^ ((lane >> 1) & 3)) << 4), w[4 * k], w[4 * k + 1], w[4 * k + 2], w[4 * k + 3]);
               fence_proxy_async_smem();              // generic-proxy writes -> visible to the TMA engine
-              named_bar_sync(1 + half, 128);
-              if (gt == 0) {
-                tma_store_2d(&tmD, box, col0, m0);
+              __syncwarp();
+              if (lane == 0) {
+                // written once, read later by other kernels: do not let it displace the W tiles being re-read from L2
+                tma_store_2d_hint(&tmD, box, col0, m0 + q * 32, store_policy);
                 bulk_commit();
               }
               ++store_seq;
@@ -400,7 +410,7 @@ umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
     }
   }
 
-  if (MODE == MODE_CE_BWD && (threadIdx.x == 128 || threadIdx.x == 256)) bulk_wait_all();   // last stores have landed   // the last tile's store has landed
+  if (MODE == MODE_CE_BWD && warp >= 4 && lane == 0) bulk_wait_all();   // this warp's last stores have landed   // the last tile's store has landed
   tc_fence_before();
   if (PAIR) cluster_sync_all(); else __syncthreads();    // neither CTA of a pair may leave while the other still needs it
   if (warp == 2) {
@@ -707,6 +717,6 @@ extern "C" int b2_lmhead_ce_bwd_dlogits(const void* H, long long ldh, const void
   p.bias = bias; p.round_bf16 = round_logits_bf16;
   p.lse = lse; p.gscale = gscale_dev; p.dlogits = static_cast<__nv_bfloat16*>(dlogits); p.ldd = ldd;
   CUtensorMap td;
-  if ((rc = make_tmap(&td, dlogits, V, rows, ldd, 32, BM, "b2_lmhead_ce_bwd_dlogits dlogits", CU_TENSOR_MAP_SWIZZLE_64B)) != B2_OK) return rc;
+  if ((rc = make_tmap(&td, dlogits, V, rows, ldd, 32, 32, "b2_lmhead_ce_bwd_dlogits dlogits", CU_TENSOR_MAP_SWIZZLE_64B)) != B2_OK) return rc;
   return launch<MODE_CE_BWD, 0, 0>(ta, tb, td, p, stream);
 }
