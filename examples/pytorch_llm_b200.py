@@ -47,8 +47,10 @@ def train_loop_per_worker(config):
     model = train.torch.prepare_model(model)
     inner = model.module if hasattr(model, "module") else model
 
-    optimizer = b200_train.AdamW(model.parameters(), lr=config["lr"], weight_decay=0.01)
-    criterion = b200_train.CrossEntropyLoss()
+    stock = config.get("stock", False)         # --stock: the reference's own torch calls, for a side-by-side timing
+    optimizer = (torch.optim.AdamW if stock else b200_train.AdamW)(model.parameters(), lr=config["lr"], weight_decay=0.01)
+    criterion = torch.nn.CrossEntropyLoss() if stock else b200_train.CrossEntropyLoss()
+    clip = torch.nn.utils.clip_grad_norm_ if stock else b200_train.clip_grad_norm_
     total = config["num_epochs"] * num_batches
     warm = int(total * config["warmup_steps_ratio"])
 
@@ -67,8 +69,10 @@ def train_loop_per_worker(config):
         for batch_idx, (inputs, targets) in enumerate(loader):
             if batch_idx >= num_batches:
                 break
+            if batch_idx == config["timing_warmup"]:
+                t_start = torch.cuda.Event(enable_timing=True); t_start.record()
             optimizer.zero_grad(set_to_none=True)
-            if config["bf16"]:
+            if config["bf16"] and not stock:
                 # hidden states -> fused LM head + CE (logits never materialised); labels are pre-shifted by the dataset
                 hidden = inner.features(inputs) if not hasattr(model, "module") else _features(model, inputs)
                 loss = b200_train.fused_lm_head_ce(hidden, inner.fc_out.weight, targets, inner.fc_out.bias, shift=False)
@@ -76,13 +80,20 @@ def train_loop_per_worker(config):
                 outputs = model(inputs)
                 loss = criterion(outputs.reshape(-1, vocab), targets.reshape(-1))
             loss.backward()
-            b200_train.clip_grad_norm_(model.parameters(), max_norm=1.0)
+            clip(model.parameters(), max_norm=1.0)
             optimizer.step()
             scheduler.step()
             step += 1
             if world_rank == 0 and (batch_idx % config["log_frequency_batches"] == 0 or batch_idx == num_batches - 1):
                 print(f"Epoch {epoch + 1}, Batch {batch_idx + 1}/{num_batches}, Step {step}, Loss: {loss.item():.4f}, "
                       f"LR: {scheduler.get_last_lr()[0]:.2e}", flush=True)
+        if num_batches > config["timing_warmup"]:
+            t_end = torch.cuda.Event(enable_timing=True); t_end.record(); torch.cuda.synchronize()
+            timed = num_batches - config["timing_warmup"]
+            ms = t_start.elapsed_time(t_end) / timed
+            if world_rank == 0:
+                print(f"TIMING {ms:.2f} ms/step, {world_size * bs * seq_len / ms * 1e3:.0f} tokens/s over {timed} steps "
+                      f"({'stock torch' if stock else 'b200_train'}, {world_size} GPU(s))", flush=True)
         metrics = {"loss": loss.item(), "epoch": epoch + 1, "learning_rate_epoch_end": scheduler.get_last_lr()[0],
                    "global_step_epoch_end": step}
         with tempfile.TemporaryDirectory() as tmp:
@@ -108,6 +119,7 @@ def main():
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--bf16", action="store_true")
     ap.add_argument("--small", action="store_true", help="BASELINE configs[0] small GPT instead of the reference's 1.2 B model")
+    ap.add_argument("--stock", action="store_true", help="use torch's AdamW / CrossEntropyLoss / clip_grad_norm_ (timing comparison)")
     ap.add_argument("--storage", default=os.path.join(tempfile.gettempdir(), "b2_runs"))
     args = ap.parse_args()
     from b200_train.train import CheckpointConfig, RunConfig, ScalingConfig, TorchConfig, TorchTrainer
@@ -116,7 +128,7 @@ def main():
     cfg = {"lr": 3e-4, "batch_size_per_worker": 16, "num_epochs": 1, **(small if args.small else big),
            "model_max_seq_len": 1024, "dataset_seq_len": 256, "log_frequency_batches": 20, "warmup_steps_ratio": 0.05,
            "min_lr_ratio": 0.01, "test_run": True, "vocab_size": 283, "n_tokens": 20000, "max_steps": args.steps,
-           "bf16": args.bf16}
+           "bf16": args.bf16, "stock": args.stock, "timing_warmup": min(5, max(0, args.steps - 2))}
     trainer = TorchTrainer(train_loop_per_worker, train_loop_config=cfg,
                            scaling_config=ScalingConfig(num_workers=args.num_workers, use_gpu=True, resources_per_worker={"GPU": 1}),
                            run_config=RunConfig(name="b200_basicllm", storage_path=args.storage,
