@@ -58,8 +58,9 @@ __device__ __forceinline__ uint64_t gtime_ns() {
   return t;
 }
 
-// Spin until *flag (written by a peer) reaches `epoch`. A peer that never arrives (crashed worker) must not
-// hang the GPU: after ~20 s record the failure in the error word and trap so the launch fails loudly.
+// Spin until *flag (written by a peer) reaches `epoch`. Ranks may legitimately be far apart (rank 0 writing a checkpoint
+// while the others already run the next backward), so the wait is long — but a peer that never arrives (crashed worker)
+// must not hang the GPU forever: after ~10 min (the order of NCCL's watchdog) record the failure and trap.
 __device__ __forceinline__ void wait_flag(const uint32_t* flag, uint32_t epoch, uint32_t* err) {
   uint64_t t0 = 0;
   uint32_t spins = 0;
@@ -67,7 +68,7 @@ __device__ __forceinline__ void wait_flag(const uint32_t* flag, uint32_t epoch, 
     if ((++spins & 0xfffu) == 0) {
       const uint64_t now = gtime_ns();
       if (t0 == 0) t0 = now;
-      else if (now - t0 > 20000000000ull) {
+      else if (now - t0 > 600000000000ull) {
         *err = 1;
         printf("b2train: peer barrier timed out waiting for epoch %u (block %d)\n", epoch, (int)blockIdx.x);
         __trap();

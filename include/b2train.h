@@ -179,7 +179,7 @@ int b2_gather_windows(const long long* tokens, long long n_tokens, const long lo
  * b2_peer_allgather: pushes this rank's slice of the buffer to every peer (used for updated parameters).
  * `epoch` must increase by one on every collective call, identically on all ranks (start at 1).
  * Every rank must enqueue the same sequence of calls; the kernels wait for one another inside the GPU, so each
- * rank needs its own device. A peer that never arrives makes the kernel trap after ~20 s instead of hanging. */
+ * rank needs its own device. A peer that never arrives makes the kernel trap after ~10 min instead of hanging. */
 size_t b2_peer_flags_bytes(void);
 int b2_symm_alloc(size_t bytes, void** dptr, unsigned char handle[64]);
 int b2_symm_open(const unsigned char handle[64], void** dptr);
