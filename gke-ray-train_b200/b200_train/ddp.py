@@ -7,8 +7,9 @@ back (so `.module` only exists when world_size > 1 — same as Ray, cf. ref :301
 
 The wrapper plays the role of torch.nn.parallel.DistributedDataParallel ($SP/torch/nn/parallel/distributed.py:655):
 `.module`, `forward`, `no_sync()`, rank-0 weights broadcast at construction. What differs is the data path: the
-gradients live in ONE flat buffer per dtype in symmetric memory, and when backward finishes a single peer-memory
-kernel per buffer (b2_peer_allreduce) averages them over NVLink — no bucket copy-in, no NCCL all-reduce, no copy-out.
+gradients live in ONE flat buffer per dtype in symmetric memory, and ranges of it ("buckets") are averaged in place over
+NVLink by our peer-memory kernel (b2_peer_allreduce / b2_peer_allreduce_mc) while the rest of backward still runs — no
+bucket copy-in, no NCCL all-reduce, no copy-out.
 """
 import contextlib
 import os
@@ -56,10 +57,10 @@ class DistributedDataParallel(nn.Module):
         self.process_group = process_group
         self.world_size = dist.get_world_size(process_group)
         self.comm = PeerComm(device, process_group)
-        self.buffers = flatten_params(params, alloc=self.comm.alloc)
+        self.flat_buffers = flatten_params(params, alloc=self.comm.alloc)   # (not `buffers`: that is nn.Module's method)
         self.shard_optimizer = bool(shard_optimizer)
         # DDP's _sync_module_states: every rank starts from rank 0's weights and buffers (bootstrap over NCCL)
-        for buf in self.buffers:
+        for buf in self.flat_buffers:
             dist.broadcast(buf.data, src=0, group=process_group)
             buf.comm = self.comm
             buf.reduced_sumsq = None
@@ -84,7 +85,7 @@ class DistributedDataParallel(nn.Module):
         self._overlap_blocks = int(os.environ.get("B2_DDP_MAX_BLOCKS", 96))
         cap_bytes = int(bucket_cap_mb * 1024 * 1024) if self.overlap else (1 << 62)      # no overlap: one launch per buffer
         self._buckets, self._bucket_of = [], {}
-        for buf in self.buffers:
+        for buf in self.flat_buffers:
             esize = buf.data.element_size()
             end = buf.numel
             members = []
@@ -151,7 +152,7 @@ class DistributedDataParallel(nn.Module):
     def _finalize_backward(self):
         """Runs once per backward pass, after the last gradient has been accumulated."""
         self._callback_queued = False
-        for buf in self.buffers:
+        for buf in self.flat_buffers:
             buf.install_grads()            # a stray .grad (allocated by autograd after a foreign zero_grad) is copied in
         self._launch_ready(force=True)     # whatever is left (all of it without overlap; unused parameters' buckets)
         if self.overlap:
@@ -168,7 +169,7 @@ class DistributedDataParallel(nn.Module):
     def forward_prepare(self):
         """Forward-side bookkeeping (gradient views in place, stale reductions forgotten). forward() calls it; call it
         yourself only when you drive `self.module` piecewise (e.g. its feature extractor + a fused loss)."""
-        for buf in self.buffers:
+        for buf in self.flat_buffers:
             missing = [i for i, p in enumerate(buf.params) if p.grad is None]
             if missing:
                 # someone dropped the gradients (zero_grad(set_to_none=True) of a stock optimizer): hand autograd

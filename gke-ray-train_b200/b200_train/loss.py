@@ -193,5 +193,7 @@ def patch_causal_lm(model, chunk_rows=DEFAULT_CHUNK_ROWS):
                                       attentions=getattr(out, "attentions", None))
 
     model.forward = forward
-    model._b2_fused_head = fused
+    # kept out of the module tree on purpose: registering it would add `_b2_fused_head.*` keys to model.state_dict()
+    # and break checkpoint compatibility with the unpatched model (ref: pytorch_llm_ray.py:301 saves state_dict())
+    object.__setattr__(model, "_b2_fused_head", fused)
     return model

@@ -110,10 +110,10 @@ def main():
     acc_opt.zero_grad(set_to_none=True)
     with acc_model.no_sync():
         acc_model(input_ids=mb[0][0], labels=mb[0][1], num_items_in_batch=n_items).loss.backward()
-    g_before = acc_model.buffers[0].grad.clone()
+    g_before = acc_model.flat_buffers[0].grad.clone()
     acc_model(input_ids=mb[1][0], labels=mb[1][1], num_items_in_batch=n_items).loss.backward()
     # after the synchronised backward every rank holds the same averaged gradient; it differs from the local partial one
-    g = acc_model.buffers[0].grad.clone()
+    g = acc_model.flat_buffers[0].grad.clone()
     g0 = g.clone(); dist.broadcast(g0, 0)
     assert torch.equal(g, g0) and not torch.equal(g, g_before)
     # and equals the mean over ranks of the locally accumulated gradients, computed the slow way

@@ -160,3 +160,15 @@ def test_trainer_shim_single_worker_inline():
 
     r = train.TorchTrainer(loop, train_loop_config={"a": 1}, scaling_config=train.ScalingConfig(num_workers=1)).fit()
     assert seen == {"rank": 0, "world": 1, "cfg": {"a": 1}} and r.metrics == {"loss": 1.5}
+
+
+def test_patch_causal_lm_keeps_state_dict_and_parameters():
+    import b200_train
+    import workloads as WL
+    m = WL.make_gpt2(dtype=torch.bfloat16, seed=0, vocab_size=101, n_embd=32, n_layer=1, n_head=2, n_positions=16)
+    keys, n_params = list(m.state_dict().keys()), len(list(m.parameters()))
+    b200_train.patch_causal_lm(m)
+    assert list(m.state_dict().keys()) == keys and len(list(m.parameters())) == n_params
+    # without labels the stock forward still answers (logits present)
+    out = m(input_ids=torch.zeros(1, 4, dtype=torch.long))
+    assert out.logits is not None and out.logits.shape == (1, 4, 101)
