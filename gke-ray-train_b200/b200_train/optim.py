@@ -45,6 +45,8 @@ class AdamW(torch.optim.Optimizer):
         self._buffers = None
         self._chunk_group = {}
         self._group_step = []      # one shared CPU step tensor per param_group (torch keeps one per parameter)
+        self._fired = set()        # parameters whose gradient was produced by a backward pass since the last step()
+        self._skip_tables = {}
         if all(p.is_cuda for g in self.param_groups for p in g["params"]):
             self._setup()           # flatten now, so the very first backward already accumulates into the flat buffer
 
@@ -72,6 +74,10 @@ class AdamW(torch.optim.Optimizer):
                     table[o // 64:(o + p.numel() + 63) // 64] = gid[id(p)]
             self._chunk_group[id(buf)] = table.to(buf.device)
             buf.optimizer_attached = True
+            for p in buf.params:
+                if id(p) in gid and not getattr(p, "_b2_step_hook", False):
+                    p.register_post_accumulate_grad_hook(self._mark_fired)
+                    p._b2_step_hook = True
             for p, o in zip(buf.params, buf.offsets):
                 if id(p) not in gid:
                     continue
@@ -80,6 +86,31 @@ class AdamW(torch.optim.Optimizer):
                     # views into the flat state: state_dict() keeps torch's per-parameter layout
                     st["exp_avg"] = buf.exp_avg[o:o + p.numel()].view(p.shape)
                     st["exp_avg_sq"] = buf.exp_avg_sq[o:o + p.numel()].view(p.shape)
+
+    def _mark_fired(self, p):
+        self._fired.add(id(p))
+
+    def _table_for(self, buf):
+        """Chunk table for this step. torch skips a parameter whose .grad is None (no decay, no state update); here
+        gradients are persistent views that are never None, so "received no gradient" is detected instead: if a backward
+        pass ran since the last step() and left some parameter untouched, its chunks are marked 255 (= skip). When no
+        backward ran at all (gradients written by hand), every parameter is treated as live."""
+        base = self._chunk_group[id(buf)]
+        if not self._fired:
+            return base
+        dead = tuple(i for i, p in enumerate(buf.params) if id(p) not in self._fired and p.requires_grad)
+        if not dead:
+            return base
+        key = (id(buf), dead)
+        t = self._skip_tables.get(key)
+        if t is None:
+            host = base.cpu().clone()
+            for i in dead:
+                o, n = buf.offsets[i], buf.params[i].numel()
+                host[o // 64:(o + n + 63) // 64] = 255
+            t = host.to(buf.device)
+            self._skip_tables[key] = t
+        return t
 
     def _share_steps(self):
         """All parameters of a group advance together, so they share one `step` tensor (saved per parameter by
@@ -131,17 +162,19 @@ class AdamW(torch.optim.Optimizer):
             hyper.append(dict(lr=g["lr"], beta1=b1, beta2=b2, eps=g["eps"], weight_decay=g["weight_decay"],
                               step=int(t.item())))
         for buf in self._buffers:
+            table = self._table_for(buf)
             if buf.shard_range is None:
-                ops.adamw_grouped_(buf.data, buf.grad, buf.exp_avg, buf.exp_avg_sq, self._chunk_group[id(buf)], hyper,
+                ops.adamw_grouped_(buf.data, buf.grad, buf.exp_avg, buf.exp_avg_sq, table, hyper,
                                    gscale=buf.pending_coef)
             else:
                 # this rank's slice only (its gradient slice is the one the reduce-scatter completed), then the updated
                 # slice is pushed to every peer's parameter buffer
                 lo, hi = buf.shard_range
                 ops.adamw_grouped_(buf.data[lo:hi], buf.grad[lo:hi], buf.exp_avg, buf.exp_avg_sq,
-                                   self._chunk_group[id(buf)][lo // 64:hi // 64], hyper, gscale=buf.pending_coef)
+                                   table[lo // 64:hi // 64], hyper, gscale=buf.pending_coef)
                 buf.comm.allgather_(buf.data)
             buf.pending_coef = None
+        self._fired = set()
         return loss
 
     def _gathered_state(self, buf):

@@ -356,3 +356,28 @@ def test_resident_window_loader_matches_reference_pipeline(b200):
     # a window that does not fit is flagged, not read out of bounds
     bad = mine.gather(torch.tensor([len(stream) - T], device=dev()))
     assert int(mine._err.item()) == 1 and int(bad[0].abs().sum()) == 0
+
+
+def test_adamw_skips_parameters_without_gradient_like_torch(b200):
+    """torch.optim.AdamW leaves a parameter whose .grad is None alone (no weight decay either); so do we."""
+    class Net(nn.Module):
+        def __init__(self):
+            super().__init__()
+            self.used = nn.Linear(32, 32)
+            self.unused = nn.Linear(32, 32)
+
+        def forward(self, x):
+            return self.used(x)
+
+    torch.manual_seed(0)
+    m_ref = Net().to(dev()); m_my = copy.deepcopy(m_ref)
+    o_ref = torch.optim.AdamW(m_ref.parameters(), lr=1e-2, weight_decay=0.1)
+    o_my = b200.AdamW(m_my.parameters(), lr=1e-2, weight_decay=0.1)
+    x = torch.randn(8, 32, device=dev())
+    for _ in range(3):
+        for m, o in ((m_ref, o_ref), (m_my, o_my)):
+            o.zero_grad(set_to_none=True)
+            m(x).pow(2).mean().backward()
+            o.step()
+    assert torch.equal(m_my.unused.weight, m_ref.unused.weight)          # untouched: bit-identical to the initial value
+    np.testing.assert_allclose(m_my.used.weight.detach().cpu().numpy(), m_ref.used.weight.detach().cpu().numpy(), atol=1e-6)
