@@ -36,6 +36,8 @@ WORKLOADS = {
     "gpt2-124m": dict(desc="gpt2-124m full fine-tune, seq 1024, bf16 (BASELINE configs[1])", b=8, t=1024, ga=1),
     "llama-1b": dict(desc="llama-3.2-1b shape full fine-tune, seq 2048, bf16, 2 sequences x 4 accumulation steps per GPU "
                           "(BASELINE configs[2])", b=2, t=2048, ga=4),
+    "llama-8b": dict(desc="llama-3-8b shape full fine-tune, 128k-vocab untied LM head, seq 2048, bf16, 1 sequence x 2 "
+                          "accumulation steps per GPU (BASELINE configs[3])", b=1, t=2048, ga=2),
 }
 
 
@@ -223,7 +225,11 @@ def run_ours(args):
     global B_PER_GPU, SEQ
     wl = WORKLOADS[args.workload]
     B_PER_GPU, SEQ, GA = wl["b"], wl["t"], wl["ga"]
-    model = TR.make_gpt2(dtype=torch.bfloat16, seed=0) if args.workload == "gpt2-124m" else TR.make_llama(dtype=torch.bfloat16, seed=0)
+    if args.workload == "gpt2-124m":
+        model = TR.make_gpt2(dtype=torch.bfloat16, seed=0)
+    else:
+        model = TR.make_llama(dtype=torch.bfloat16, seed=0, device=device,
+                              **(TR.LLAMA_8B if args.workload == "llama-8b" else {}))
     model.train()
     stock = args.impl == "stock-gpu"       # informational third arm: the reference's stock torch path on THIS GPU
     if stock:

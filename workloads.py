@@ -153,8 +153,11 @@ def make_gpt2(dtype=torch.bfloat16, seed=0, **overrides):
     return GPT2LMHeadModel(cfg).to(dtype)
 
 
-def make_llama(dtype=torch.bfloat16, seed=0, **overrides):
-    """Llama-3.2-1B shape by default (BASELINE configs[2]); `tie_word_embeddings=False, hidden_size=4096, ...` gives 8B."""
+def make_llama(dtype=torch.bfloat16, seed=0, device=None, **overrides):
+    """Llama-3.2-1B shape by default (BASELINE configs[2]); `tie_word_embeddings=False, hidden_size=4096, ...` gives 8B.
+    `device`: build (and randomly initialise) the parameters directly there — an 8 B-parameter model takes minutes to
+    initialise on host cores and seconds on the GPU."""
+    import contextlib
     from transformers import LlamaConfig, LlamaForCausalLM
     torch.manual_seed(seed)
     kw = dict(vocab_size=128256, hidden_size=2048, intermediate_size=8192, num_hidden_layers=16,
@@ -163,6 +166,10 @@ def make_llama(dtype=torch.bfloat16, seed=0, **overrides):
     kw.update(overrides)
     cfg = LlamaConfig(**kw)
     cfg.use_cache = False
-    return LlamaForCausalLM(cfg).to(dtype)
+    with (torch.device(device) if device is not None else contextlib.nullcontext()):
+        model = LlamaForCausalLM(cfg)
+    return model.to(dtype)
 
 
+LLAMA_8B = dict(hidden_size=4096, intermediate_size=14336, num_hidden_layers=32, num_attention_heads=32,
+                num_key_value_heads=8, head_dim=128, tie_word_embeddings=False)      # BASELINE configs[3]
