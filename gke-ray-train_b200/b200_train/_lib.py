@@ -70,6 +70,7 @@ _SIGS = {
                                      ctypes.c_uint, c_int, c_int, c_int, c_void_p]),
     "b2_peer_allgather": (c_int, [c_void_p, c_void_p, c_int, c_int, c_size_t, c_size_t, c_int, ctypes.c_uint, c_void_p]),
     "b2_peer_slice": (c_int, [c_size_t, c_int, c_int, c_int, c_void_p, c_void_p]),
+    "b2_debug_peer_copy": (c_int, [c_void_p, c_void_p, c_size_t, c_int, c_int, c_int, c_void_p]),
 }
 
 for _name, (_res, _args) in _SIGS.items():

@@ -31,6 +31,20 @@ def get_device():
     return torch.device("cuda", int(os.environ.get("LOCAL_RANK", "0")) % torch.cuda.device_count())
 
 
+def plan_buckets(offsets, total, esize, cap_bytes):
+    """Cuts a flat buffer (parameter start offsets `offsets`, `total` elements, `esize` bytes each) into contiguous
+    ranges from its END, each closed as soon as it holds at least `cap_bytes`; the last one takes whatever is left at the
+    front. Returns [(start, numel, [parameter indices])] in launch order (last parameters first)."""
+    out, end, members = [], total, []
+    for i in range(len(offsets) - 1, -1, -1):
+        members.append(i)
+        start = offsets[i] if i > 0 else 0
+        if (end - start) * esize >= cap_bytes or i == 0:
+            out.append((start, end - start, members))
+            end, members = start, []
+    return out
+
+
 class _Bucket:
     """A contiguous element range of one flat gradient buffer, reduced by one kernel launch."""
     __slots__ = ("buf", "offset", "numel", "nparams", "pending")
@@ -86,18 +100,10 @@ class DistributedDataParallel(nn.Module):
         cap_bytes = int(bucket_cap_mb * 1024 * 1024) if self.overlap else (1 << 62)      # no overlap: one launch per buffer
         self._buckets, self._bucket_of = [], {}
         for buf in self.flat_buffers:
-            esize = buf.data.element_size()
-            end = buf.numel
-            members = []
-            for i in range(len(buf.params) - 1, -1, -1):
-                members.append(i)
-                start = buf.offsets[i]
-                if (end - start) * esize >= cap_bytes or i == 0:
-                    b = _Bucket(buf, start, end - start, len(members))
-                    for j in members:
-                        self._bucket_of[id(buf.params[j])] = len(self._buckets)
-                    self._buckets.append(b)
-                    end, members = start, []
+            for start, numel, members in plan_buckets(buf.offsets, buf.numel, buf.data.element_size(), cap_bytes):
+                for j in members:
+                    self._bucket_of[id(buf.params[j])] = len(self._buckets)
+                self._buckets.append(_Bucket(buf, start, numel, len(members)))
         self._next_bucket = 0
         self._comm_stream = torch.cuda.Stream(device=device) if self.overlap else None
         for p in params:

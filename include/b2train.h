@@ -199,6 +199,11 @@ int b2_peer_allgather(void* const* peer_bufs, uint32_t* const* peer_flags, int w
                       size_t n, int dtype, unsigned epoch, b2_stream_t stream);
 int b2_peer_slice(size_t n, int dtype, int world, int rank, size_t* begin, size_t* end);
 
+/* ---- measurement aid (tools/peer_probe.py; no counterpart in the reference) -----------------------------------
+ * Raw one-directional copy between a local and a peer-mapped buffer with a chosen load flavour (0 ld.relaxed.sys,
+ * 1 plain ld.global, 2 ld.volatile), unroll (1/2/4/8) and grid: what the NVLink path sustains from a kernel. */
+int b2_debug_peer_copy(const void* src, void* dst, size_t bytes, int unroll, int flavour, int blocks, b2_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -172,3 +172,21 @@ def test_patch_causal_lm_keeps_state_dict_and_parameters():
     # without labels the stock forward still answers (logits present)
     out = m(input_ids=torch.zeros(1, 4, dtype=torch.long))
     assert out.logits is not None and out.logits.shape == (1, 4, 101)
+
+
+def test_bucket_plan_covers_the_buffer_in_reverse_order():
+    from b200_train.ddp import plan_buckets
+    from b200_train.flat import TOTAL_MULTIPLE
+    offsets = [0, 64, 1088, 1152, 9344]                  # 64-aligned parameter starts
+    total = TOTAL_MULTIPLE                                # padded buffer length
+    plan = plan_buckets(offsets, total, 2, cap_bytes=4096)
+    # contiguous, disjoint, covering [0, total), launched from the end towards the front
+    assert plan[0][0] + plan[0][1] == total and plan[-1][0] == 0
+    for (s0, n0, _), (s1, n1, _) in zip(plan, plan[1:]):
+        assert s1 + n1 == s0
+    assert sorted(i for _, _, m in plan for i in m) == list(range(len(offsets)))
+    assert all(s % 64 == 0 and n % 8 == 0 for s, n, _ in plan)
+    # every bucket but the front one reaches the cap
+    assert all(n * 2 >= 4096 for _, n, _ in plan[:-1])
+    # one bucket when the cap is huge (the no-overlap / sharded path)
+    assert plan_buckets(offsets, total, 2, 1 << 62) == [(0, total, [4, 3, 2, 1, 0])]

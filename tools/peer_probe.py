@@ -20,9 +20,6 @@ def main():
     dist.init_process_group("nccl", device_id=dev)
     from b200_train import _lib
     from b200_train.symm import PeerComm
-    _lib.lib.b2_debug_peer_copy.restype = ctypes.c_int
-    _lib.lib.b2_debug_peer_copy.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_size_t, ctypes.c_int, ctypes.c_int,
-                                            ctypes.c_int, ctypes.c_void_p]
     comm = PeerComm(dev)
     nbytes = 1 << 30
     t = comm.alloc(nbytes // 2, torch.bfloat16, dev)
