@@ -499,7 +499,10 @@ extern "C" int b2_peer_allreduce_mc(void* mc_buf, void* const* peer_bufs, uint32
   size_t v0, v1;
   slice_of(n / per_vec, world, rank, v0, v1);
   if (want_sumsq == 1) peer_zero_sumsq_kernel<<<1, 32, 0, stream>>>(pp.flags[rank]);
-  const unsigned grid = peer_grid(v1 - v0, max_blocks);
+  // the switch does the adding: a few dozen CTAs keep it busy, more only contend (measured at W = 8: 32 CTAs 842 GB/s,
+  // 296 CTAs 800 GB/s on 2 GiB; profiles/README.md)
+  const int mc_cap = 32;
+  const unsigned grid = peer_grid(v1 - v0, (max_blocks > 0 && max_blocks < mc_cap) ? max_blocks : mc_cap);
   if (dtype == B2_BF16) {
     if (scatter_only) peer_allreduce_mc_kernel<B2_BF16, true><<<grid, 512, 0, stream>>>(pp, mc, world, rank, v0, v1, scale, epoch, want_sumsq);
     else peer_allreduce_mc_kernel<B2_BF16, false><<<grid, 512, 0, stream>>>(pp, mc, world, rank, v0, v1, scale, epoch, want_sumsq);

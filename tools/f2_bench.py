@@ -37,6 +37,7 @@ def main():
     ap.add_argument("--log2n", type=int, nargs="+", default=[20, 24, 27, 30])
     ap.add_argument("--iters", type=int, default=7)
     ap.add_argument("--tail", action="store_true")
+    ap.add_argument("--sweep-blocks", type=int, nargs="*", default=[], help="also time the all-reduce on capped grids")
     args = ap.parse_args()
     rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
     dev = torch.device("cuda", local)
@@ -58,7 +59,10 @@ def main():
         ms_nccl = timed(lambda: dist.all_reduce(ref), args.iters, dev)
         bus = 2.0 * (world - 1) / world * n * 2
         row = {"n": n, "bytes": 2 * n, "world": world, "peer_ms": ms_peer, "nccl_ms": ms_nccl,
-               "peer_busbw_GBs": bus / ms_peer / 1e6, "nccl_busbw_GBs": bus / ms_nccl / 1e6}
+               "peer_busbw_GBs": bus / ms_peer / 1e6, "nccl_busbw_GBs": bus / ms_nccl / 1e6, "nvls": bool(comm.use_nvls)}
+        for nb in args.sweep_blocks:
+            ms = timed(lambda: comm.allreduce_(t, want_sumsq=True, max_blocks=nb), args.iters, dev)
+            row[f"peer_busbw_GBs_blocks{nb}"] = bus / ms / 1e6
         if args.tail and l2 >= 24:
             # fused tail: F2 (with sum of squares) -> clip coefficient -> fused AdamW
             p = (torch.randn(n, device=dev)).to(torch.bfloat16)
