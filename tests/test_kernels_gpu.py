@@ -303,3 +303,18 @@ def test_gemm_split_k_matches_unsplit(ops):
     C3 = torch.ones(M, N, dtype=torch.float32, device=dev())
     ops.gemm_bf16(A, B, C3, M, N, K, b_mn_major=True, accumulate=True)
     assert ((C3 - 1 - ref).abs() <= 1e-3 * ref.abs().max()).all()
+
+
+def test_empty_inputs(ops):
+    """Zero rows / zero elements are legal everywhere: no launch over nothing, torch's conventions for the results."""
+    H = torch.zeros(0, 64, dtype=torch.bfloat16, device=dev())
+    W = torch.zeros(32, 64, dtype=torch.bfloat16, device=dev())
+    y = torch.zeros(0, dtype=torch.int64, device=dev())
+    r = ops.lmhead_ce_fwd(H, W, y)
+    assert int(r.n_valid.item()) == 0 and float(r.loss_sum.item()) == 0.0 and np.isnan(r.loss_mean.item())
+    r = ops.ce_rows_fwd(torch.zeros(0, 7, device=dev()), y)
+    assert int(r.n_valid.item()) == 0 and np.isnan(r.loss_mean.item())
+    e = torch.zeros(0, device=dev())
+    assert float(ops.sumsq(e).item()) == 0.0
+    ops.adamw_(e, e, e.clone(), e.clone(), lr=1e-3, step=1)          # no-op, must not fail
+    ops.scale_(e, torch.ones(1, device=dev()))
