@@ -176,16 +176,7 @@ class DistributedDataParallel(nn.Module):
         """Forward-side bookkeeping (gradient views in place, stale reductions forgotten). forward() calls it; call it
         yourself only when you drive `self.module` piecewise (e.g. its feature extractor + a fused loss)."""
         for buf in self.flat_buffers:
-            missing = [i for i, p in enumerate(buf.params) if p.grad is None]
-            if missing:
-                # someone dropped the gradients (zero_grad(set_to_none=True) of a stock optimizer): hand autograd
-                # zero-filled views of the flat buffer again so it accumulates in place
-                if len(missing) == len(buf.params):
-                    buf.grad.zero_()
-                else:
-                    for i in missing:
-                        buf.grad_view(i).zero_()
-                buf.install_grads()
+            buf.ensure_grads()
             buf.reduced_sumsq = None
 
     @contextlib.contextmanager

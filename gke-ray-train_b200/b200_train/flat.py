@@ -67,6 +67,20 @@ class FlatBuffer:
                 moved += 1
         return moved
 
+    def ensure_grads(self):
+        """Before a forward/backward pass: if someone dropped gradients (a foreign `zero_grad(set_to_none=True)`, e.g.
+        HF Trainer's `model.zero_grad()`), hand autograd zero-filled views of the flat buffer again so that it accumulates
+        in place instead of allocating (and later copying) 100+ separate tensors."""
+        missing = [i for i, p in enumerate(self.params) if p.grad is None]
+        if not missing:
+            return
+        if len(missing) == len(self.params):
+            self.grad.zero_()
+        else:
+            for i in missing:
+                self.grad_view(i).zero_()
+        self.install_grads()
+
     def zero_grad(self):
         self.grad.zero_()
         self.pending_coef = None

@@ -12,6 +12,7 @@ import torch.nn as nn
 
 from . import ops
 from ._lib import B2Error
+from .flat import buffers_of
 
 DEFAULT_CHUNK_ROWS = 8192
 
@@ -185,6 +186,11 @@ def patch_causal_lm(model, chunk_rows=DEFAULT_CHUNK_ROWS):
             return orig_forward(input_ids=input_ids, labels=labels, **kw)
         kw.pop("return_dict", None)
         kw.pop("logits_to_keep", None)
+        if torch.is_grad_enabled():
+            # parameters that live in a flat buffer (b200_train.AdamW / prepare_model): keep autograd accumulating into
+            # it even if the caller dropped the gradients with a plain model.zero_grad() (HF Trainer does, every step)
+            for buf in buffers_of(model.parameters())[0]:
+                buf.ensure_grads()
         out = backbone(input_ids=input_ids, **kw)
         hidden = out[0]
         loss = fused(hidden, labels, num_items_in_batch=num_items_in_batch)

@@ -381,3 +381,25 @@ def test_adamw_skips_parameters_without_gradient_like_torch(b200):
             o.step()
     assert torch.equal(m_my.unused.weight, m_ref.unused.weight)          # untouched: bit-identical to the initial value
     np.testing.assert_allclose(m_my.used.weight.detach().cpu().numpy(), m_ref.used.weight.detach().cpu().numpy(), atol=1e-6)
+
+
+def test_foreign_zero_grad_keeps_flat_gradients(b200):
+    """HF Trainer calls model.zero_grad() (gradients -> None) every step; the patched forward re-installs the flat views so
+    the step still matches the stock path and no per-parameter gradient tensors are allocated."""
+    ref_model = _tiny_gpt2().train()
+    my_model = b200.patch_causal_lm(copy.deepcopy(ref_model)).train()
+    before = {n: p.detach().clone() for n, p in ref_model.named_parameters()}
+    ref_opt = torch.optim.AdamW(TR.hf_param_groups(ref_model, 1e-3), lr=2e-4)
+    my_opt = b200.AdamW(TR.hf_param_groups(my_model, 1e-3), lr=2e-4)
+    ids, lab = TR.synthetic_hf_batch(4, 64, 2003, seed=77, device=dev())
+    for _ in range(2):
+        ref_model.zero_grad(); my_model.zero_grad()                      # set_to_none=True is torch's default
+        assert all(p.grad is None for p in my_model.parameters())
+        ref_model(input_ids=ids, labels=lab).loss.backward()
+        my_model(input_ids=ids, labels=lab).loss.backward()
+        buf = my_opt.flat_buffers()[0]
+        assert all(p.grad.data_ptr() == buf.grad_view(i).data_ptr() for i, p in enumerate(buf.params))
+        torch.nn.utils.clip_grad_norm_(ref_model.parameters(), 0.3); ref_opt.step()
+        b200.clip_grad_norm_(my_model.parameters(), 0.3); my_opt.step()
+    for (n, a), (_, b) in zip(my_model.named_parameters(), ref_model.named_parameters()):
+        _bf16_close(a, b, before[n], n, steps=2)
