@@ -81,11 +81,14 @@ class CrossEntropyLoss(nn.Module):
 
 class _LMHeadCEFn(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, hidden, weight, bias, labels, shift_T, ignore_index, reduction, num_items, round_bf16, chunk_rows):
+    def forward(ctx, hidden, weight, bias, labels, shift_T, ignore_index, reduction, num_items, round_bf16, chunk_rows,
+                check_labels=False):
         H = hidden if hidden.stride(-1) == 1 else hidden.contiguous()
         bias32 = None if bias is None else bias.detach().to(torch.float32).contiguous()
         r = ops.lmhead_ce_fwd(H, weight, labels, bias=bias32, shift_T=shift_T, ignore_index=ignore_index,
                               round_logits_bf16=round_bf16)
+        if check_labels and int(r.err.item()):          # one host sync; torch raises here, by default we poison the loss
+            raise IndexError("Target out of bounds for the LM-head loss (label outside [0, V) and != ignore_index)")
         ctx.save_for_backward(H, weight, labels, r.lse, r.n_valid)
         ctx.bias32, ctx.has_bias = bias32, bias is not None
         ctx.bias_dtype = None if bias is None else bias.dtype
@@ -127,17 +130,18 @@ class _LMHeadCEFn(torch.autograd.Function):
             dW = dW.to(W.dtype)
         if db is not None:
             db = db.to(ctx.bias_dtype)
-        return dH, dW, db, None, None, None, None, None, None, None
+        return dH, dW, db, None, None, None, None, None, None, None, None
 
 
 def fused_lm_head_ce(hidden, weight, labels, bias=None, *, shift=True, ignore_index=-100, reduction="mean",
-                     num_items_in_batch=None, round_logits_bf16=True, chunk_rows=DEFAULT_CHUNK_ROWS):
+                     num_items_in_batch=None, round_logits_bf16=True, chunk_rows=DEFAULT_CHUNK_ROWS, check_labels=False):
     """loss = CE(hidden @ weight.T (+bias), labels) without materialising the logits.
 
     hidden [..., T, D] bf16, weight [V, D] bf16, labels [..., T] int64. shift=True applies the causal shift inside
     (row t is scored against labels[t+1], the last position ignored) exactly as HF's ForCausalLMLoss; shift=False
     expects pre-shifted labels (the reference's TextDataset, ref: ray-jobs/pytorch_llm_ray.py:116-119).
-    num_items_in_batch: HF gradient-accumulation normaliser — the loss is sum / num_items_in_batch."""
+    num_items_in_batch: HF gradient-accumulation normaliser — the loss is sum / num_items_in_batch.
+    check_labels=True raises IndexError on an out-of-range label like torch (one host sync); otherwise the loss is NaN."""
     if hidden.dtype != torch.bfloat16 or weight.dtype != torch.bfloat16:
         raise B2Error("fused_lm_head_ce takes bfloat16 hidden states and weight (use CrossEntropyLoss for fp32 logits)")
     T = hidden.shape[-2] if hidden.dim() >= 2 else 1
@@ -146,7 +150,7 @@ def fused_lm_head_ce(hidden, weight, labels, bias=None, *, shift=True, ignore_in
     if y.device != H2.device:
         y = y.to(H2.device)
     return _LMHeadCEFn.apply(H2, weight, bias, y, T if shift else 0, ignore_index, reduction, num_items_in_batch,
-                             round_logits_bf16, chunk_rows)
+                             round_logits_bf16, chunk_rows, check_labels)
 
 
 class FusedLMHeadCE(nn.Module):

@@ -403,3 +403,13 @@ def test_foreign_zero_grad_keeps_flat_gradients(b200):
         b200.clip_grad_norm_(my_model.parameters(), 0.3); my_opt.step()
     for (n, a), (_, b) in zip(my_model.named_parameters(), ref_model.named_parameters()):
         _bf16_close(a, b, before[n], n, steps=2)
+
+
+def test_out_of_range_label_raises_when_asked(b200):
+    H = torch.zeros(4, 64, dtype=torch.bfloat16, device=dev()); W = torch.zeros(16, 64, dtype=torch.bfloat16, device=dev())
+    y = torch.tensor([[0, 1, 16, 2]], device=dev())
+    with pytest.raises(IndexError):
+        b200.fused_lm_head_ce(H.view(1, 4, 64), W, y, shift=False, check_labels=True)
+    with pytest.raises(IndexError):
+        b200.CrossEntropyLoss(check_labels=True)(torch.zeros(4, 16, device=dev()), y.reshape(-1))
+    assert torch.isnan(b200.fused_lm_head_ce(H.view(1, 4, 64), W, y, shift=False))        # default: poisoned, no sync
