@@ -180,6 +180,8 @@ def f1_roofline(torch, b200, model, device, peaks, iters=5):
             "kernel": "umma_kernel family per step: fused LM-head+CE forward, dlogits recompute, dH GEMM, dW GEMM "
                       "(timed together through autograd; 6*N*V*D algorithmic flop, 8*N*V*D executed)",
             "ms": ms, "algorithmic_flops": flops, "launches": parts,
+            # the same 6*N*V*D over the SUM of the four launch durations (no host gaps, no combine/finalize/reduce helpers)
+            "achieved_sum_of_launches": flops / (sum(v["ms"] for v in parts.values()) * 1e-3) / 1e12,
             "peak_source": peaks["source"] + ", burst bf16 GEMM"}
 
 
