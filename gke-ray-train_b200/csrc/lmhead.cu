@@ -16,11 +16,15 @@
 //   MODE_CE_FWD  per (row, vocab split): (max, sumexp) partials + label logit
 //   MODE_CE_BWD  dlogits[row, col] = (exp(logit - lse[row]) - [col == label]) * gscale   (0 for ignored rows)
 //
-// Tile 128 (M) x 256 (N) x 64 (K), tcgen05.mma cta_group::1 kind::f16 M=128 N=256 K=16, fp32 accumulators
-// double-buffered in TMEM (2 x 256 columns) so the epilogue of tile i overlaps the MMAs of tile i+1.
-// Warp roles (256 threads, 1 CTA/SM, persistent over work units): warp 0 = TMA producer, warp 1 = MMA issuer,
-// warp 2 = TMEM allocator, warps 4-7 = epilogue (one TMEM lane = one row per thread).
-// Tensor-bound: algorithmic flops = 2*M*N*K per pass.
+// Tile 128 (M) x 256 (N) x 64 (K) per CTA, tcgen05.mma kind::f16 (bf16 in, fp32 out), fp32 accumulators double-buffered
+// in TMEM (2 x 256 columns) so the epilogue of tile i overlaps the MMAs of tile i+1. Two shapes of the same template:
+//   single CTAs (cta_group::1, M=128 N=256 K=16; 4-stage 48 KiB operand ring)         -> the two cross-entropy kernels
+//   CTA pairs   (cta_group::2, M=256: each CTA holds its 128 rows of A and half of B;  -> the plain GEMMs
+//                6-stage 32 KiB ring; the leader issues the MMAs and multicasts the commits)
+// Warp roles (384 threads, 1 CTA/SM, persistent over work units): warp 0 = TMA producer, warp 1 = MMA issuer (one thread),
+// warp 2 = TMEM allocator, warps 4-11 = epilogue (warp w owns TMEM lane quarter w%4 and one 128-column half; one thread =
+// one row). The dlogits epilogue leaves through 64B-swizzled shared memory and TMA stores, one 32x32 block per warp.
+// Tensor-bound: algorithmic flops = 2*M*N*K per pass (measurements in profiles/README.md).
 #include "b2_common.cuh"
 #include "umma.cuh"
 #include <math.h>
