@@ -10,7 +10,6 @@ calls, a collate and a pinned-memory copy.
 import torch
 from torch.utils.data import DistributedSampler
 
-from . import _lib
 from ._lib import B2Error, call, ptr, stream_ptr
 
 

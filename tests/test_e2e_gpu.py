@@ -338,7 +338,7 @@ def test_optimizer_state_dict_roundtrip_matches_torch(b200):
 def test_resident_window_loader_matches_reference_pipeline(b200):
     """Batch for batch identical (integers: bit-exact) to TextDataset -> Subset -> DataLoader(shuffle, drop_last) ->
     prepare_data_loader's DistributedSampler, for both ranks of a 2-worker job."""
-    from torch.utils.data import DataLoader, DistributedSampler, Subset, TensorDataset
+    from torch.utils.data import DataLoader, DistributedSampler, TensorDataset
     stream = TR.synthetic_char_stream(5000, 283)
     T, B, limit = 64, 16, 1000
     for rank in (0, 1):

@@ -6,8 +6,6 @@ Collected last on purpose (the file name sorts after every other test file), so 
 everything else when it gets here. Works in a fresh process and after the other tests alike: it needs no state from
 them and leaves none behind.
 """
-import ctypes
-
 import numpy as np
 import pytest
 import torch

@@ -1,7 +1,6 @@
 """What does the NVLink path sustain from a kernel? (torchrun, 2+ ranks). Rank 0 copies between its own memory and
 rank 1's, in each direction, with different load flavours / unrolls / grids; also both directions at once (rank 0
 and rank 1 active together)."""
-import ctypes
 import os
 import sys
 

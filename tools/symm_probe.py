@@ -1,6 +1,6 @@
 """Can torch's symmetric-memory allocator give us peer pointers and an NVLS multicast address on this box? (torchrun)"""
 import os
-import sys
+
 import torch
 import torch.distributed as dist
 
