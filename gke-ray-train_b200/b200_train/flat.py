@@ -40,6 +40,7 @@ class FlatBuffer:
                 view.copy_(p.data)
                 p.data = view
                 p._b2_flat = (self, o)
+        self._views = None
         self.install_grads()
         # set by clip_grad_norm_ when an attached optimizer will apply the coefficient inside its kernel
         self.pending_coef = None
@@ -49,22 +50,29 @@ class FlatBuffer:
         self.exp_avg_sq = None
 
     def grad_view(self, i):
-        p, o = self.params[i], self.offsets[i]
-        return self.grad[o:o + p.numel()].view(p.shape)
+        """The slice of the flat gradient buffer that is parameter i's .grad (one persistent tensor object per parameter:
+        building 100+ views on every call would cost the host about a millisecond per step)."""
+        if self._views is None:
+            self._views = [self.grad[o:o + p.numel()].view(p.shape) for p, o in zip(self.params, self.offsets)]
+        return self._views[i]
 
     def install_grads(self):
         """(Re-)point every parameter's .grad at its slice of the flat gradient buffer. A .grad that autograd
         allocated on its own since (after a zero_grad(set_to_none=True) issued elsewhere) is copied in first."""
         moved = 0
-        for i, p in enumerate(self.params):
-            want = self.grad_view(i)
+        self.grad_view(0) if self.params else None
+        for p, want in zip(self.params, self._views or ()):
             g = p.grad
+            if g is want:
+                continue
             if g is None:
                 p.grad = want
             elif g.data_ptr() != want.data_ptr():
                 want.copy_(g)
                 p.grad = want
                 moved += 1
+            else:
+                p.grad = want          # same memory through another tensor object: adopt ours
         return moved
 
     def ensure_grads(self):

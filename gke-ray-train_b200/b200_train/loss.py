@@ -193,7 +193,11 @@ def patch_causal_lm(model, chunk_rows=DEFAULT_CHUNK_ROWS):
         if torch.is_grad_enabled():
             # parameters that live in a flat buffer (b200_train.AdamW / prepare_model): keep autograd accumulating into
             # it even if the caller dropped the gradients with a plain model.zero_grad() (HF Trainer does, every step)
-            for buf in buffers_of(model.parameters())[0]:
+            bufs = model.__dict__.get("_b2_flat_cache")
+            if not bufs:                               # discovered once the optimizer / prepare_model has flattened them
+                bufs = buffers_of(model.parameters())[0]
+                model.__dict__["_b2_flat_cache"] = bufs
+            for buf in bufs:
                 buf.ensure_grads()
         out = backbone(input_ids=input_ids, **kw)
         hidden = out[0]
