@@ -12,7 +12,7 @@ import torch
 
 from . import ops
 from ._lib import B2Error
-from .flat import buffers_of
+from .flat import buffers_of, flat_of
 
 
 @torch.no_grad()
@@ -24,12 +24,20 @@ def clip_grad_norm_(parameters, max_norm, norm_type=2.0, error_if_nonfinite=Fals
         raise B2Error("b200_train.clip_grad_norm_ implements the 2-norm the reference uses")
     if not params:
         return torch.tensor(0.0)
-    bufs, loose = buffers_of(params)
     device = params[0].grad.device
-    covered = {id(p) for p in params}
+    # fast path (the usual call: every parameter of the model, all of them living in the same flat buffers, in buffer
+    # order): a few identity checks instead of rebuilding the parameter -> buffer map on every step
+    f0 = flat_of(params[0])
+    bufs = loose = None
+    if f0 is not None and len(params) == len(f0[0].params) and all(a is b for a, b in zip(params, f0[0].params)):
+        bufs, loose, whole_all = [f0[0]], [], True
+    else:
+        bufs, loose = buffers_of(params)
+        whole_all = False
+    covered = None if whole_all else {id(p) for p in params}
     pieces = []
     for buf in bufs:
-        whole = all(id(p) in covered for p in buf.params)
+        whole = whole_all or all(id(p) in covered for p in buf.params)
         reduced = getattr(buf, "reduced_sumsq", None)
         if whole and reduced is not None:
             pieces.append(reduced)          # already produced by the all-reduce kernel's epilogue: no extra pass
@@ -59,7 +67,7 @@ def clip_grad_norm_(parameters, max_norm, norm_type=2.0, error_if_nonfinite=Fals
         raise RuntimeError(f"The total norm of order {norm_type} for gradients from `parameters` is non-finite, "
                            "so it cannot be clipped.")
     for buf in bufs:
-        whole = all(id(p) in covered for p in buf.params)
+        whole = whole_all or all(id(p) in covered for p in buf.params)
         if whole and buf.optimizer_attached:
             buf.pending_coef = coef                             # consumed by the next AdamW.step()
         elif whole:

@@ -76,7 +76,9 @@ class AdamW(torch.optim.Optimizer):
             buf.optimizer_attached = True
             for p in buf.params:
                 if id(p) in gid and not getattr(p, "_b2_step_hook", False):
-                    p.register_post_accumulate_grad_hook(self._mark_fired)
+                    # the hook is the set's own C-level `add` (no Python frame per parameter on the autograd thread);
+                    # the set object therefore has to stay the same one for the optimizer's lifetime (cleared, not replaced)
+                    p.register_post_accumulate_grad_hook(self._fired.add)
                     p._b2_step_hook = True
             for p, o in zip(buf.params, buf.offsets):
                 if id(p) not in gid:
@@ -87,9 +89,6 @@ class AdamW(torch.optim.Optimizer):
                     st["exp_avg"] = buf.exp_avg[o:o + p.numel()].view(p.shape)
                     st["exp_avg_sq"] = buf.exp_avg_sq[o:o + p.numel()].view(p.shape)
 
-    def _mark_fired(self, p):
-        self._fired.add(id(p))
-
     def _table_for(self, buf):
         """Chunk table for this step. torch skips a parameter whose .grad is None (no decay, no state update); here
         gradients are persistent views that are never None, so "received no gradient" is detected instead: if a backward
@@ -98,7 +97,7 @@ class AdamW(torch.optim.Optimizer):
         base = self._chunk_group[id(buf)]
         if not self._fired:
             return base
-        dead = tuple(i for i, p in enumerate(buf.params) if id(p) not in self._fired and p.requires_grad)
+        dead = tuple(i for i, p in enumerate(buf.params) if p not in self._fired and p.requires_grad)
         if not dead:
             return base
         key = (id(buf), dead)
@@ -174,7 +173,7 @@ class AdamW(torch.optim.Optimizer):
                                    table[lo // 64:hi // 64], hyper, gscale=buf.pending_coef)
                 buf.comm.allgather_(buf.data)
             buf.pending_coef = None
-        self._fired = set()
+        self._fired.clear()
         return loss
 
     def _gathered_state(self, buf):
