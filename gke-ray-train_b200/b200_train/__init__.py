@@ -10,6 +10,7 @@ from ._lib import B2Error  # noqa: F401
 __version__ = "0.1.0"
 from .clip import clip_grad_norm_  # noqa: E402,F401
 from .ddp import DistributedDataParallel, get_device, prepare_model  # noqa: E402,F401
+from .comm_hook import PeerAllreduceState, peer_allreduce_hook  # noqa: E402,F401
 from .loss import CrossEntropyLoss, FusedLMHeadCE, fused_lm_head_ce, patch_causal_lm  # noqa: E402,F401
 from .optim import AdamW  # noqa: E402,F401
 from . import train  # noqa: E402,F401

@@ -190,3 +190,16 @@ def test_bucket_plan_covers_the_buffer_in_reverse_order():
     assert all(n * 2 >= 4096 for _, n, _ in plan[:-1])
     # one bucket when the cap is huge (the no-overlap / sharded path)
     assert plan_buckets(offsets, total, 2, 1 << 62) == [(0, total, [4, 3, 2, 1, 0])]
+
+
+def test_comm_hook_state_refuses_to_exist_without_group_or_gpu():
+    """The communication hook for stock DDP has no CPU path and needs the process group."""
+    import inspect
+    import b200_train
+    with pytest.raises(b200_train.B2Error):
+        b200_train.PeerAllreduceState()                       # no process group
+    # torch's register_comm_hook checks the hook's annotations; ours carries none, and takes (state, bucket)
+    sig = inspect.signature(b200_train.peer_allreduce_hook)
+    assert list(sig.parameters) == ["state", "bucket"]
+    assert all(p.annotation is inspect.Parameter.empty for p in sig.parameters.values())
+    assert sig.return_annotation is inspect.Signature.empty

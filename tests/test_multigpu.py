@@ -18,3 +18,14 @@ def test_peer_memory_ddp(world):
            "--master-addr", "127.0.0.1", "--master-port", str(29600 + world), os.path.join(HERE, "mp_peer_worker.py")]
     r = subprocess.run(cmd, capture_output=True, text=True, timeout=600)
     assert r.returncode == 0 and "MP_OK" in r.stdout, r.stdout[-3000:] + r.stderr[-3000:]
+
+
+@pytest.mark.parametrize("world", [2, 4, 8])
+def test_comm_hook_on_stock_ddp(world):
+    """b200_train.peer_allreduce_hook behind torch DDP's own register_comm_hook == the default all-reduce."""
+    if torch.cuda.device_count() < world:
+        pytest.skip(f"needs {world} GPUs")
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={world}",
+           "--master-addr", "127.0.0.1", "--master-port", str(29700 + world), os.path.join(HERE, "mp_hook_worker.py")]
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0 and "HOOK_OK" in r.stdout, r.stdout[-3000:] + r.stderr[-3000:]
