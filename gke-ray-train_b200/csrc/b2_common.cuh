@@ -68,6 +68,14 @@ __device__ __forceinline__ uint32_t pack_bf16(float lo, float hi) {
   return *reinterpret_cast<uint32_t*>(&t);
 }
 __device__ __forceinline__ float round_bf16(float x) { return __bfloat162float(__float2bfloat16_rn(x)); }
+// Two values rounded to bf16 precision (round-to-nearest-even, same result as round_bf16 on each) through ONE packed
+// conversion (F2FP.BF16.F32.PACK_AB) plus two integer ops. The scalar form is an F2F per value, and F2F issues on the
+// quarter-rate XU pipe that also serves MUFU.EX2 — in the softmax epilogues that pipe is the limiter.
+__device__ __forceinline__ void round_bf16_pair(float& a, float& b) {
+  const uint32_t w = pack_bf16(a, b);
+  a = bf16_lo(w);
+  b = bf16_hi(w);
+}
 
 // load / store 8 consecutive elements of dtype f32 or bf16 as floats
 template <int DT> struct Vec8;

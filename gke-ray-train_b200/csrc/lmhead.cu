@@ -337,7 +337,7 @@ umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
             }
             if (p.round_bf16) {
 #pragma unroll
-              for (int j = 0; j < 32; ++j) x[j] = round_bf16(x[j]);
+              for (int j = 0; j < 32; j += 2) round_bf16_pair(x[j], x[j + 1]);
             }
 
             if (MODE == MODE_CE_FWD) {
