@@ -157,11 +157,18 @@ def f1_roofline(torch, b200, model, device, peaks, iters=5):
     dH = torch.empty(N, D, dtype=torch.bfloat16, device=device)
     dW = torch.empty(V, D, dtype=torch.bfloat16, device=device)
     gs = torch.full((1,), 1.0 / N, device=device)
+    from b200_train import loss as L
+    keep = L._KEEP_LOGITS and N <= L.DEFAULT_CHUNK_ROWS and N * ldd * 2 <= L._KEEP_LOGITS_MAX_BYTES   # the route the loss takes
+    recompute = lambda: ops.lmhead_ce_bwd_dlogits(Hd, Wd, y, r.lse, gs, 0, N, dl, shift_T=SEQ)   # noqa: E731
+    if keep:
+        route = (("forward", lambda: ops.lmhead_ce_fwd(Hd, Wd, y, shift_T=SEQ, keep_logits=dl)),
+                 ("dlogits", lambda: ops.ce_dlogits_inplace_(dl, y, r.lse, gs, 0, N, V, shift_T=SEQ)))
+    else:
+        route = (("forward", lambda: ops.lmhead_ce_fwd(Hd, Wd, y, shift_T=SEQ)), ("dlogits", recompute))
     parts = {}
-    for name, fn in (("forward", lambda: ops.lmhead_ce_fwd(Hd, Wd, y, shift_T=SEQ)),
-                     ("dlogits", lambda: ops.lmhead_ce_bwd_dlogits(Hd, Wd, y, r.lse, gs, 0, N, dl, shift_T=SEQ)),
-                     ("dH", lambda: ops.gemm_bf16(dl, Wd, dH, N, D, V, b_mn_major=True)),
-                     ("dW", lambda: ops.gemm_bf16(dl, Hd, dW, V, D, N, a_mn_major=True, b_mn_major=True))):
+    for name, fn in route + (("dH", lambda: ops.gemm_bf16(dl, Wd, dH, N, D, V, b_mn_major=True)),
+                             ("dW", lambda: ops.gemm_bf16(dl, Hd, dW, V, D, N, a_mn_major=True, b_mn_major=True)),
+                             ("dlogits_recompute_route", recompute)):
         ts = []
         for it in range(iters + 1):
             flush.fill_(it & 0xff)
@@ -171,13 +178,27 @@ def f1_roofline(torch, b200, model, device, peaks, iters=5):
             if it >= 1:
                 ts.append(e0.elapsed_time(e1))
         t = sum(ts) / len(ts)
-        parts[name] = {"ms": t, "tflops": 2.0 * N * V * D / (t * 1e-3) / 1e12}
+        if keep and name == "dlogits":      # not a GEMM: one read + one write of the [N, V] bf16 matrix
+            parts[name] = {"ms": t, "gbs": 4.0 * N * V / (t * 1e-3) / 1e9, "bound": "hbm"}
+        else:
+            parts[name] = {"ms": t, "tflops": 2.0 * N * V * D / (t * 1e-3) / 1e12}
+    other = parts.pop("dlogits_recompute_route")
+    if keep:
+        kernel = ("umma_kernel family per step: fused LM-head+CE forward that keeps its bf16 logits, in-place soft-max "
+                  "gradient (HBM-bound, no tensor cores), dH GEMM, dW GEMM (timed together through autograd; "
+                  "6*N*V*D algorithmic flop = executed flop)")
+    else:
+        kernel = ("umma_kernel family per step: fused LM-head+CE forward, dlogits recompute, dH GEMM, dW GEMM "
+                  "(timed together through autograd; 6*N*V*D algorithmic flop, 8*N*V*D executed)")
     return {"bound": "tensor", "achieved": achieved, "peak": peaks["bf16_tflops"], "unit": "TFLOP/s",
             "frac": achieved / peaks["bf16_tflops"],
-            "traffic": 3.13e9,   # dram read+write summed over the family's 4 launches, ncu --set full (profiles/README.md)
-            "kernel": "umma_kernel family per step: fused LM-head+CE forward, dlogits recompute, dH GEMM, dW GEMM "
-                      "(timed together through autograd; 6*N*V*D algorithmic flop, 8*N*V*D executed)",
-            "ms": ms, "algorithmic_flops": flops, "launches": parts,
+            # dram read+write summed over the family's launches from ncu --set full (profiles/README.md): measured for the
+            # recompute route only (3.13e9); the kept-logits route has not been captured yet
+            "traffic": None if keep else 3.13e9,
+            "traffic_recompute_route": 3.13e9,
+            "route": "kept-logits" if keep else "recompute",
+            "kernel": kernel,
+            "ms": ms, "algorithmic_flops": flops, "launches": parts, "dlogits_recompute_route": other,
             # the same 6*N*V*D over the SUM of the four launch durations (no host gaps, no combine/finalize/reduce helpers)
             "achieved_sum_of_launches": flops / (sum(v["ms"] for v in parts.values()) * 1e-3) / 1e12,
             "peak_source": peaks["source"] + ", burst bf16 GEMM"}

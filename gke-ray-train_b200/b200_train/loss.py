@@ -7,6 +7,8 @@
   (ref: ray-jobs/fine_tune_llama_ray.py:333 -> $SP/transformers/models/llama/modeling_llama.py:486-491 ->
   $SP/transformers/loss/loss_utils.py:45-67).
 """
+import os
+
 import torch
 import torch.nn as nn
 
@@ -15,6 +17,11 @@ from ._lib import B2Error
 from .flat import buffers_of
 
 DEFAULT_CHUNK_ROWS = 8192
+# Keep the forward's bf16 logits for the backward when they fit one chunk (B2_KEEP_LOGITS=0: always recompute them;
+# B2_KEEP_LOGITS_MAX_MB bounds the buffer, default 4096 MiB — it replaces the d(logits) chunk buffer of the same size,
+# but lives from the head's forward to its backward instead of only during the backward).
+_KEEP_LOGITS = os.environ.get("B2_KEEP_LOGITS", "1") != "0"
+_KEEP_LOGITS_MAX_BYTES = int(float(os.environ.get("B2_KEEP_LOGITS_MAX_MB", "4096")) * (1 << 20))
 
 
 def _gscale(grad_out, result, reduction, num_items):
@@ -85,8 +92,17 @@ class _LMHeadCEFn(torch.autograd.Function):
                 check_labels=False):
         H = hidden if hidden.stride(-1) == 1 else hidden.contiguous()
         bias32 = None if bias is None else bias.detach().to(torch.float32).contiguous()
+        # One chunk of rows and a gradient wanted: let the forward leave its bf16 logits in the buffer the backward would
+        # otherwise fill by a second pass over the tensor cores; the backward then rewrites them in place (HBM-bound).
+        N, V = H.shape[0], weight.shape[0]
+        ldd = (V + 7) // 8 * 8
+        kept = None
+        if (_KEEP_LOGITS and round_bf16 and 0 < N <= chunk_rows and any(ctx.needs_input_grad[:3])
+                and N * ldd * 2 <= _KEEP_LOGITS_MAX_BYTES):
+            kept = torch.empty(N, ldd, dtype=torch.bfloat16, device=H.device)
         r = ops.lmhead_ce_fwd(H, weight, labels, bias=bias32, shift_T=shift_T, ignore_index=ignore_index,
-                              round_logits_bf16=round_bf16)
+                              round_logits_bf16=round_bf16, keep_logits=kept)
+        ctx.kept = kept
         if check_labels and int(r.err.item()):          # one host sync; torch raises here, by default we poison the loss
             raise IndexError("Target out of bounds for the LM-head loss (label outside [0, V) and != ignore_index)")
         ctx.save_for_backward(H, weight, labels, r.lse, r.n_valid)
@@ -105,7 +121,12 @@ class _LMHeadCEFn(torch.autograd.Function):
         gs = _gscale(grad_out, ctx.result, reduction, num_items)
         ldd = (V + 7) // 8 * 8
         chunk = min(N, chunk_rows)
-        dl = torch.empty(chunk, ldd, dtype=torch.bfloat16, device=H.device)
+        kept, ctx.kept = ctx.kept, None
+        if kept is None and getattr(ctx, "kept_used", False):
+            raise B2Error("this LM-head loss was already back-propagated once: its kept logits were turned into the "
+                          "gradient in place. Set B2_KEEP_LOGITS=0 to back-propagate the same graph twice")
+        ctx.kept_used = kept is not None
+        dl = kept if kept is not None else torch.empty(chunk, ldd, dtype=torch.bfloat16, device=H.device)
         need_dH, need_dW = ctx.needs_input_grad[0], ctx.needs_input_grad[1]
         dH = torch.empty(N, D, dtype=torch.bfloat16, device=H.device) if need_dH else None
         n_chunks = (N + chunk - 1) // chunk
@@ -118,8 +139,11 @@ class _LMHeadCEFn(torch.autograd.Function):
         for c in range(n_chunks):
             r0 = c * chunk
             rows = min(chunk, N - r0)
-            ops.lmhead_ce_bwd_dlogits(H, W, labels, lse, gs, r0, rows, dl, bias=ctx.bias32, shift_T=shift_T,
-                                      ignore_index=ignore_index, round_logits_bf16=round_bf16)
+            if kept is not None:        # (single chunk by construction)
+                ops.ce_dlogits_inplace_(dl, labels, lse, gs, r0, rows, V, shift_T=shift_T, ignore_index=ignore_index)
+            else:
+                ops.lmhead_ce_bwd_dlogits(H, W, labels, lse, gs, r0, rows, dl, bias=ctx.bias32, shift_T=shift_T,
+                                          ignore_index=ignore_index, round_logits_bf16=round_bf16)
             if need_dH:     # dH[rows, D] = dL[rows, V] @ W[V, D]      (B = W read MN-major)
                 ops.gemm_bf16(dl, W, dH[r0:r0 + rows], rows, D, V, a_mn_major=False, b_mn_major=True)
             if need_dW:     # dW[V, D] += dL^T[V, rows] @ H[rows, D]   (A = dL and B = H both read MN-major)

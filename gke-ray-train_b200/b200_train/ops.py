@@ -163,8 +163,10 @@ def _check_hw(H, W, bias):
         raise B2Error("bias must be a contiguous float32 [V] tensor")
 
 
-def lmhead_ce_fwd(H, W, labels, bias=None, shift_T=0, ignore_index=-100, round_logits_bf16=True):
-    """Fused logits = H @ W.T (+bias) and cross-entropy; logits are never materialised."""
+def lmhead_ce_fwd(H, W, labels, bias=None, shift_T=0, ignore_index=-100, round_logits_bf16=True, keep_logits=None):
+    """Fused logits = H @ W.T (+bias) and cross-entropy. The logits are not materialised, unless `keep_logits`
+    (bf16 [N, ld >= V], ld % 8 == 0) is given: then the bf16-rounded logits are also left there, for
+    ce_dlogits_inplace_ (a backward without a second tensor-core pass)."""
     _check_hw(H, W, bias)
     N, D = H.shape
     V = W.shape[0]
@@ -173,10 +175,36 @@ def lmhead_ce_fwd(H, W, labels, bias=None, shift_T=0, ignore_index=-100, round_l
     with torch.cuda.device(H.device):
         ws_bytes = _lib.lib.b2_lmhead_ce_workspace_bytes(N)
         ws = torch.empty(max(ws_bytes, 16), dtype=torch.uint8, device=H.device)
-        call("b2_lmhead_ce_fwd", ptr(H), H.stride(0), ptr(W), W.stride(0), ptr(bias), ptr(labels), N, D, V,
-             int(shift_T), int(ignore_index), int(bool(round_logits_bf16)), ptr(ws), ws_bytes, ptr(lse), ptr(zt),
-             ptr(loss), ptr(n_valid), ptr(err), stream_ptr())
+        if keep_logits is None:
+            call("b2_lmhead_ce_fwd", ptr(H), H.stride(0), ptr(W), W.stride(0), ptr(bias), ptr(labels), N, D, V,
+                 int(shift_T), int(ignore_index), int(bool(round_logits_bf16)), ptr(ws), ws_bytes, ptr(lse), ptr(zt),
+                 ptr(loss), ptr(n_valid), ptr(err), stream_ptr())
+        else:
+            if not round_logits_bf16:
+                raise B2Error("keep_logits stores bf16 logits: it needs round_logits_bf16=True")
+            _check_logits_buffer(keep_logits, N, V, H.device)
+            call("b2_lmhead_ce_fwd_keep", ptr(H), H.stride(0), ptr(W), W.stride(0), ptr(bias), ptr(labels), N, D, V,
+                 int(shift_T), int(ignore_index), ptr(ws), ws_bytes, ptr(lse), ptr(zt), ptr(loss), ptr(n_valid),
+                 ptr(err), ptr(keep_logits), keep_logits.stride(0), stream_ptr())
     return CEResult(lse, zt, loss, n_valid, err)
+
+
+def _check_logits_buffer(t, rows, V, device):
+    if (t.dtype != torch.bfloat16 or t.dim() != 2 or t.stride(1) != 1 or t.shape[0] < rows or t.shape[1] < V
+            or t.stride(0) % 8 or t.device != device):
+        raise B2Error("logits buffer must be bfloat16 [>= rows, >= V] on the same device, unit inner stride, "
+                      "row pitch a multiple of 8")
+
+
+def ce_dlogits_inplace_(logits, labels, lse, gscale, row0, rows, V, shift_T=0, ignore_index=-100):
+    """Turns the kept bf16 logits of rows [row0, row0+rows) (`logits` starts at row row0) into d(logits), in place —
+    the same values lmhead_ce_bwd_dlogits would write."""
+    require_cuda(logits, labels, lse, gscale)
+    _check_logits_buffer(logits, rows, V, logits.device)
+    with torch.cuda.device(logits.device):
+        call("b2_ce_dlogits_inplace", ptr(logits), logits.stride(0), ptr(labels), int(row0), int(rows), int(V),
+             int(shift_T), int(ignore_index), ptr(lse), ptr(gscale), stream_ptr())
+    return logits
 
 
 def lmhead_ce_bwd_dlogits(H, W, labels, lse, gscale, row0, rows, out, bias=None, shift_T=0, ignore_index=-100,

@@ -77,6 +77,17 @@ __device__ __forceinline__ void round_bf16_pair(float& a, float& b) {
   b = bf16_hi(w);
 }
 
+__device__ __forceinline__ float fast_exp2(float x) {
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+// Exponent offset of the fused soft-max gradient: exp2(x * log2e + off) == exp(x - lse) * |gs|. One definition, so
+// that every kernel producing d(logits) rounds this the same way.
+__device__ __forceinline__ float ce_bwd_exp_offset(float gs, float lse) {
+  return fmaf(-lse, 1.4426950408889634f, log2f(fabsf(gs)));
+}
+
 // load / store 8 consecutive elements of dtype f32 or bf16 as floats
 template <int DT> struct Vec8;
 template <> struct Vec8<B2_F32> {

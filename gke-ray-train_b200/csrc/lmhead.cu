@@ -49,9 +49,9 @@ constexpr int A_STAGE_BYTES = BM * BK * 2;            // 16 KiB: this CTA's 128 
 constexpr int b_stage_bytes(bool pair) { return (pair ? BN / 2 : BN) * BK * 2; }
 constexpr int stage_bytes(bool pair) { return A_STAGE_BYTES + b_stage_bytes(pair); }
 constexpr int stages_for(bool pair) { return pair ? 6 : 4; }                 // 192 KiB of operand ring either way
-constexpr int STAGING_BYTES = 8 * 2 * 32 * 64;        // MODE_CE_BWD: 8 epilogue warps x 2 alternating [32 rows x 64 B] blocks
+constexpr int STAGING_BYTES = 8 * 2 * 32 * 64;        // storing modes: 8 epilogue warps x 2 alternating [32 rows x 64 B] blocks
 constexpr int smem_bytes_for(int mode, bool pair) {  // + 1 KiB slack to reach 1024-byte alignment
-  return stages_for(pair) * stage_bytes(pair) + 1024 + (mode == 2 ? STAGING_BYTES : 0);
+  return stages_for(pair) * stage_bytes(pair) + 1024 + (mode == 2 || mode == 3 ? STAGING_BYTES : 0);
 }
 constexpr int BOX_MN_BYTES = 64 * BK * 2;             // one MN-major TMA box: 64 K-rows x 128 B
 constexpr uint32_t TMEM_COLS = 512;
@@ -59,7 +59,11 @@ constexpr int MAX_SPLITS = 64;
 #define B2_GEMM_MAX_KSPLIT 6
 constexpr float LOG2E = 1.4426950408889634f;
 
-enum { MODE_GEMM = 0, MODE_CE_FWD = 1, MODE_CE_BWD = 2 };
+enum { MODE_GEMM = 0, MODE_CE_FWD = 1, MODE_CE_BWD = 2, MODE_CE_FWD_KEEP = 3 };
+// MODE_CE_FWD_KEEP: forward that ALSO leaves the bf16-rounded logits in memory, for the backward that transforms them in
+// place (b2_ce_dlogits_inplace) instead of recomputing the GEMM
+constexpr bool mode_is_fwd(int m) { return m == MODE_CE_FWD || m == MODE_CE_FWD_KEEP; }
+constexpr bool mode_stores(int m) { return m == MODE_CE_BWD || m == MODE_CE_FWD_KEEP; }   // tiles leave through TMA stores
 
 struct Params {
   int M, N, K;                       // rows (tokens), columns (vocab or features), reduction extent
@@ -74,12 +78,6 @@ struct Params {
   float2* part; long long part_stride; float* zt;
   const float* lse; const float* gscale; __nv_bfloat16* dlogits; long long ldd;
 };
-
-__device__ __forceinline__ float fast_exp2(float x) {
-  float y;
-  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
-  return y;
-}
 
 __device__ __forceinline__ long long label_at(const Params& p, long long i) {
   if (p.shift_T <= 0) return p.labels[i];
@@ -130,7 +128,7 @@ umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
   uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
 
-  if (threadIdx.x == 0) { tma_prefetch_desc(&tmA); tma_prefetch_desc(&tmB); if (MODE == MODE_CE_BWD) tma_prefetch_desc(&tmD); }
+  if (threadIdx.x == 0) { tma_prefetch_desc(&tmA); tma_prefetch_desc(&tmB); if (mode_stores(MODE)) tma_prefetch_desc(&tmD); }
   const int crank = PAIR ? (int)cluster_ctarank() : 0;      // 0 = leader of the pair (issues the MMAs)
   const int cid = (int)blockIdx.x / NC, ncl = (int)gridDim.x / NC;   // this CTA('s pair) and the number of them
   if (threadIdx.x == 32) {
@@ -227,7 +225,7 @@ umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
     const int half = (warp - 4) >> 2;               // 0: tile columns [0,128)   1: [128,256)
     const int trow = q * 32 + lane;                 // row inside the tile
     int as = 0; uint32_t aphase = 0;
-    uint32_t store_seq = 0;                         // MODE_CE_BWD: staging box toggle
+    uint32_t store_seq = 0;                         // storing modes: staging box toggle
     const uint64_t store_policy = l2_policy_evict_first();
     for (int u = cid; u < num_units; u += ncl) {
       const Unit t = decode_unit(p, u);
@@ -246,7 +244,7 @@ umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
         if (MODE == MODE_CE_BWD) {
           const bool valid = (y != p.ignore_index) && y >= 0 && y < p.N;
           gs = valid ? __ldg(p.gscale) : 0.f;
-          if (gs != 0.f) bwd_off = log2f(fabsf(gs)) - p.lse[p.row0 + row] * LOG2E;
+          if (gs != 0.f) bwd_off = ce_bwd_exp_offset(gs, p.lse[p.row0 + row]);
           if (!valid) y = -1;
         }
       }
@@ -258,8 +256,8 @@ umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
         for (int cc = 0; cc < BN / 64; ++cc) {
           const int c = half * (BN / 64) + cc;       // 32-column chunk of the tile handled by this thread
           const int col0 = nb * BN + c * 32;
-          if (MODE != MODE_CE_BWD && col0 >= p.N) break;   // warp-uniform: nothing but padding from here on
-          if (MODE == MODE_CE_BWD) {
+          if (!mode_stores(MODE) && col0 >= p.N) break;    // warp-uniform: nothing but padding from here on
+          if (mode_stores(MODE)) {
             // d(logits) leaves through shared memory: each warp stages its own [32 rows x 32 columns] bf16 block (2 KiB,
             // 64B-swizzled) and one lane hands it to the TMA engine (coalesced store, clipped at the matrix edge by the
             // tensor map). Two blocks per warp alternate; nothing here synchronises across warps.
@@ -271,6 +269,27 @@ umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
           uint32_t r[32];
           tmem_ld_32x32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(as * BN + c * 32), r);
           tmem_ld_wait();
+
+          // storing modes: this thread's 32 values (one row of the warp's [32 x 32] block) -> 64B-swizzled staging box ->
+          // one TMA store per warp
+          auto store_block = [&](const float (&v)[32]) {
+            uint32_t w[16];
+#pragma unroll
+            for (int j = 0; j < 32; j += 2) w[j >> 1] = pack_bf16(v[j], v[j + 1]);
+            uint8_t* box = smem + STAGES * STAGE_BYTES + ((warp - 4) * 2 + (int)(store_seq & 1)) * (32 * 64);
+            uint8_t* rowp = box + lane * 64;
+#pragma unroll
+            for (int k = 0; k < 4; ++k)               // 16-byte chunk k of the 64-byte row, SWIZZLE_64B: k ^ ((row >> 1) & 3)
+              st_shared_v4(rowp + ((k ^ ((lane >> 1) & 3)) << 4), w[4 * k], w[4 * k + 1], w[4 * k + 2], w[4 * k + 3]);
+            fence_proxy_async_smem();                // generic-proxy writes -> visible to the TMA engine
+            __syncwarp();
+            if (lane == 0) {
+              // written once, read later by other kernels: do not let it displace the W tiles being re-read from L2
+              tma_store_2d_hint(&tmD, box, col0, m0 + q * 32, store_policy);
+              bulk_commit();
+            }
+            ++store_seq;
+          };
 
           if (MODE == MODE_GEMM) {
             if (p.c_dtype == 99) {
@@ -340,7 +359,11 @@ umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
               for (int j = 0; j < 32; j += 2) round_bf16_pair(x[j], x[j + 1]);
             }
 
-            if (MODE == MODE_CE_FWD) {
+            if (mode_is_fwd(MODE)) {
+              if (MODE == MODE_CE_FWD_KEEP) {
+                // the rounded logits themselves, before the padding columns are masked (the store clips them anyway)
+                store_block(x);
+              }
               if (col0 + 32 > p.N) {                 // last chunk of the vocabulary: mask the padding columns
 #pragma unroll
                 for (int j = 0; j < 32; ++j) if (col0 + j >= p.N) x[j] = -INFINITY;
@@ -379,22 +402,7 @@ umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
 #pragma unroll
                 for (int j = 0; j < 32; ++j) d[j] = -d[j];
               }
-              uint32_t w[16];
-#pragma unroll
-              for (int j = 0; j < 32; j += 2) w[j >> 1] = pack_bf16(d[j], d[j + 1]);
-              uint8_t* box = smem + STAGES * STAGE_BYTES + ((warp - 4) * 2 + (int)(store_seq & 1)) * (32 * 64);
-              uint8_t* rowp = box + lane * 64;
-#pragma unroll
-              for (int k = 0; k < 4; ++k)             // 16-byte chunk k of the 64-byte row, SWIZZLE_64B: k ^ ((row >> 1) & 3)
-                st_shared_v4(rowp + ((k ^ ((lane >> 1) & 3)) << 4), w[4 * k], w[4 * k + 1], w[4 * k + 2], w[4 * k + 3]);
-              fence_proxy_async_smem();              // generic-proxy writes -> visible to the TMA engine
-              __syncwarp();
-              if (lane == 0) {
-                // written once, read later by other kernels: do not let it displace the W tiles being re-read from L2
-                tma_store_2d_hint(&tmD, box, col0, m0 + q * 32, store_policy);
-                bulk_commit();
-              }
-              ++store_seq;
+              store_block(d);
             }
           }
         }
@@ -406,7 +414,7 @@ umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
         as ^= 1; if (as == 0) aphase ^= 1;
       }
 
-      if (MODE == MODE_CE_FWD && row_ok) {
+      if (mode_is_fwd(MODE) && row_ok) {
         // the two column halves of a unit are merged later like any two vocabulary splits
         p.part[(long long)(2 * s + half) * p.part_stride + row] = make_float2(run_m, run_s);
         if (z_found) p.zt[row] = zval;
@@ -414,7 +422,7 @@ umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
     }
   }
 
-  if (MODE == MODE_CE_BWD && warp >= 4 && lane == 0) bulk_wait_all();   // this warp's last stores have landed   // the last tile's store has landed
+  if (mode_stores(MODE) && warp >= 4 && lane == 0) bulk_wait_all();   // this warp's last stores have landed   // the last tile's store has landed
   tc_fence_before();
   if (PAIR) cluster_sync_all(); else __syncthreads();    // neither CTA of a pair may leave while the other still needs it
   if (warp == 2) {
@@ -436,6 +444,59 @@ __global__ void __launch_bounds__(256) ce_combine_kernel(const float2* __restric
     m = nm;
   }
   lse[row] = m + logf(s);
+}
+
+// Backward from KEPT logits: x[row, col] (bf16, rounded logits left by MODE_CE_FWD_KEEP) becomes, in place,
+//   (exp(x - lse[row]) - [col == label]) * gscale          — the same arithmetic, in the same order, as the MODE_CE_BWD
+// epilogue, so the two routes give the same bits. HBM-bound: one read and one write of the [rows, V] bf16 matrix.
+// grid.y strides over rows, grid.x * block over the 16-byte vectors of a row.
+__global__ void __launch_bounds__(256) ce_dlogits_inplace_kernel(__nv_bfloat16* __restrict__ x, long long ld,
+                                                                 const long long* __restrict__ labels, long long row0,
+                                                                 long long rows, int V, int shift_T, long long ignore_index,
+                                                                 const float* __restrict__ lse,
+                                                                 const float* __restrict__ gscale) {
+  const int nvec = (V + 7) >> 3;
+  const float g = __ldg(gscale);
+  for (long long row = blockIdx.y; row < rows; row += gridDim.y) {
+    const long long i = row0 + row;
+    long long y = (shift_T <= 0) ? labels[i] : (((i % shift_T) + 1 < shift_T) ? labels[i + 1] : ignore_index);
+    const bool valid = (y != ignore_index) && y >= 0 && y < V;
+    const float gs = valid ? g : 0.f;
+    const float off = (gs != 0.f) ? ce_bwd_exp_offset(gs, lse[i]) : -INFINITY;
+    const int yv = valid ? (int)(y >> 3) : -1, ye = (int)(y & 7);
+    uint4* rp = reinterpret_cast<uint4*>(x + row * ld);
+    // four independent 16-byte loads per thread before any arithmetic: enough bytes in flight to cover HBM latency
+    for (int v0 = blockIdx.x * (blockDim.x * 4) + threadIdx.x; v0 < nvec; v0 += gridDim.x * (blockDim.x * 4)) {
+      uint4 uu[4];
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        const int v = v0 + k * (int)blockDim.x;
+        if (v < nvec) uu[k] = rp[v];
+      }
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        const int v = v0 + k * (int)blockDim.x;
+        if (v >= nvec) break;
+        const uint4 u = uu[k];
+        float f[8] = {bf16_lo(u.x), bf16_hi(u.x), bf16_lo(u.y), bf16_hi(u.y), bf16_lo(u.z), bf16_hi(u.z), bf16_lo(u.w), bf16_hi(u.w)};
+#pragma unroll
+        for (int e = 0; e < 8; ++e) f[e] = fast_exp2(fmaf(f[e], LOG2E, off));
+        if (v == yv) {
+#pragma unroll
+          for (int e = 0; e < 8; ++e) if (e == ye) f[e] -= fabsf(gs);
+        }
+        if (gs < 0.f) {
+#pragma unroll
+          for (int e = 0; e < 8; ++e) f[e] = -f[e];
+        }
+        if (v * 8 + 8 > V) {                         // the row's last vector: columns >= V are padding, left as zeros
+#pragma unroll
+          for (int e = 0; e < 8; ++e) if (v * 8 + e >= V) f[e] = 0.f;
+        }
+        rp[v] = make_uint4(pack_bf16(f[0], f[1]), pack_bf16(f[2], f[3]), pack_bf16(f[4], f[5]), pack_bf16(f[6], f[7]));
+      }
+    }
+  }
 }
 
 // C[M,N] (+)= sum over splits of ws[k][M][ldws]; 4 columns per thread
@@ -667,10 +728,12 @@ extern "C" size_t b2_lmhead_ce_workspace_bytes(long long N) {
   return (size_t)2 * MAX_SPLITS * (size_t)npad * sizeof(float2);   // (max, sumexp) per row, split and column half
 }
 
-extern "C" int b2_lmhead_ce_fwd(const void* H, long long ldh, const void* W, long long ldw, const float* bias,
-                                const long long* labels, long long N, int D, int V, int shift_T, long long ignore_index,
-                                int round_logits_bf16, void* workspace, size_t workspace_bytes, float* lse, float* zt,
-                                float* loss_out, long long* n_valid_out, int* err_out, cudaStream_t stream) {
+// logits_out == nullptr: the plain forward (MODE_CE_FWD); otherwise the forward that also stores the rounded logits
+static int lmhead_ce_fwd_impl(const void* H, long long ldh, const void* W, long long ldw, const float* bias,
+                              const long long* labels, long long N, int D, int V, int shift_T, long long ignore_index,
+                              int round_logits_bf16, void* workspace, size_t workspace_bytes, float* lse, float* zt,
+                              float* loss_out, long long* n_valid_out, int* err_out, void* logits_out, long long ldl,
+                              cudaStream_t stream) {
   B2_REQUIRE(N >= 0 && D >= 1 && V >= 1, "b2_lmhead_ce_fwd: bad shape N=%lld D=%d V=%d", N, D, V);
   B2_REQUIRE(N < (1ll << 31) - BM, "b2_lmhead_ce_fwd: N too large");
   B2_REQUIRE(loss_out && n_valid_out, "b2_lmhead_ce_fwd: null output");
@@ -692,11 +755,56 @@ extern "C" int b2_lmhead_ce_fwd(const void* H, long long ldh, const void* W, lon
     p.labels = labels; p.shift_T = shift_T; p.ignore_index = ignore_index; p.row0 = 0;
     p.bias = bias; p.round_bf16 = round_logits_bf16;
     p.part = static_cast<float2*>(workspace); p.part_stride = (N + BM - 1) / BM * BM; p.zt = zt;
-    if ((rc = launch<MODE_CE_FWD, 0, 0>(ta, tb, ta, p, stream)) != B2_OK) return rc;
+    if (logits_out == nullptr) {
+      if ((rc = launch<MODE_CE_FWD, 0, 0>(ta, tb, ta, p, stream)) != B2_OK) return rc;
+    } else {
+      CUtensorMap td;
+      if ((rc = make_tmap(&td, logits_out, V, N, ldl, 32, 32, "b2_lmhead_ce_fwd_keep logits", CU_TENSOR_MAP_SWIZZLE_64B)) != B2_OK) return rc;
+      if ((rc = launch<MODE_CE_FWD_KEEP, 0, 0>(ta, tb, td, p, stream)) != B2_OK) return rc;
+    }
     ce_combine_kernel<<<(unsigned)((N + 255) / 256), 256, 0, stream>>>(p.part, p.part_stride, 2 * p.n_splits, N, lse);
     B2_CHECK_CUDA(cudaGetLastError());
   }
   return b2_ce_finalize_launch(lse, zt, labels, N, V, shift_T, ignore_index, loss_out, n_valid_out, err_out, stream);
+}
+
+extern "C" int b2_lmhead_ce_fwd(const void* H, long long ldh, const void* W, long long ldw, const float* bias,
+                                const long long* labels, long long N, int D, int V, int shift_T, long long ignore_index,
+                                int round_logits_bf16, void* workspace, size_t workspace_bytes, float* lse, float* zt,
+                                float* loss_out, long long* n_valid_out, int* err_out, cudaStream_t stream) {
+  return lmhead_ce_fwd_impl(H, ldh, W, ldw, bias, labels, N, D, V, shift_T, ignore_index, round_logits_bf16, workspace,
+                            workspace_bytes, lse, zt, loss_out, n_valid_out, err_out, nullptr, 0, stream);
+}
+
+extern "C" int b2_lmhead_ce_fwd_keep(const void* H, long long ldh, const void* W, long long ldw, const float* bias,
+                                     const long long* labels, long long N, int D, int V, int shift_T,
+                                     long long ignore_index, void* workspace, size_t workspace_bytes, float* lse,
+                                     float* zt, float* loss_out, long long* n_valid_out, int* err_out, void* logits_out,
+                                     long long ldl, cudaStream_t stream) {
+  B2_REQUIRE(logits_out != nullptr || N == 0, "b2_lmhead_ce_fwd_keep: null logits buffer");
+  B2_REQUIRE(ldl >= V && ldl % 8 == 0, "b2_lmhead_ce_fwd_keep: ldl must be >= V and a multiple of 8");
+  B2_REQUIRE(b2_aligned(logits_out, 16), "b2_lmhead_ce_fwd_keep: logits buffer must be 16-byte aligned");
+  // the kept values are the bf16-rounded logits, so the loss must be computed from exactly those: rounding is implied
+  return lmhead_ce_fwd_impl(H, ldh, W, ldw, bias, labels, N, D, V, shift_T, ignore_index, 1, workspace, workspace_bytes,
+                            lse, zt, loss_out, n_valid_out, err_out, N == 0 ? nullptr : logits_out, ldl, stream);
+}
+
+extern "C" int b2_ce_dlogits_inplace(void* logits, long long ldl, const long long* labels, long long row0, long long rows,
+                                     int V, int shift_T, long long ignore_index, const float* lse,
+                                     const float* gscale_dev, cudaStream_t stream) {
+  if (rows == 0) return B2_OK;
+  B2_REQUIRE(rows > 0 && row0 >= 0 && V >= 1, "b2_ce_dlogits_inplace: bad shape rows=%lld V=%d", rows, V);
+  B2_REQUIRE(logits && labels && lse && gscale_dev, "b2_ce_dlogits_inplace: null buffer");
+  B2_REQUIRE(ldl >= V && ldl % 8 == 0, "b2_ce_dlogits_inplace: ldl must be >= V and a multiple of 8");
+  B2_REQUIRE(b2_aligned(logits, 16), "b2_ce_dlogits_inplace: logits buffer must be 16-byte aligned");
+  const int nvec = (V + 7) / 8;
+  // 4 vectors (64 B) per thread and row; rows are dealt to grid.y (at most 65535 of them, strided beyond that)
+  const unsigned gx = (unsigned)((nvec + 256 * 4 - 1) / (256 * 4));
+  const unsigned gy = (unsigned)(rows < 65535 ? rows : 65535);
+  ce_dlogits_inplace_kernel<<<dim3(gx, gy), 256, 0, stream>>>(static_cast<__nv_bfloat16*>(logits), ldl, labels, row0, rows,
+                                                             V, shift_T, ignore_index, lse, gscale_dev);
+  B2_CHECK_CUDA(cudaGetLastError());
+  return B2_OK;
 }
 
 extern "C" int b2_lmhead_ce_bwd_dlogits(const void* H, long long ldh, const void* W, long long ldw, const float* bias,

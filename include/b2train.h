@@ -125,6 +125,24 @@ int b2_lmhead_ce_fwd(const void* H, long long ldh, const void* W, long long ldw,
                      const long long* labels, long long N, int D, int V, int shift_T, long long ignore_index,
                      int round_logits_bf16, void* workspace, size_t workspace_bytes, float* lse, float* zt,
                      float* loss_out, long long* n_valid_out, int* err_out, b2_stream_t stream);
+/* Forward that also KEEPS the logits: as b2_lmhead_ce_fwd with round_logits_bf16 = 1, and additionally stores the
+ * bf16-rounded logits (the values the loss was computed from) to logits_out [N, ldl] (ldl >= V, ldl % 8 == 0, 16-byte
+ * aligned; columns [V, ldl) are padding and are not written). For callers that can afford N * ldl * 2 bytes between
+ * forward and backward: the backward then needs no second pass over the tensor cores, see b2_ce_dlogits_inplace.
+ * Same reference lines as b2_lmhead_ce_fwd — there the materialised tensor is `logits` itself
+ * ($SP/transformers/models/llama/modeling_llama.py:486; fp32 copy at $SP/transformers/loss/loss_utils.py:57). */
+int b2_lmhead_ce_fwd_keep(const void* H, long long ldh, const void* W, long long ldw, const float* bias,
+                          const long long* labels, long long N, int D, int V, int shift_T, long long ignore_index,
+                          void* workspace, size_t workspace_bytes, float* lse, float* zt, float* loss_out,
+                          long long* n_valid_out, int* err_out, void* logits_out, long long ldl, b2_stream_t stream);
+/* Backward from kept logits, in place: logits[r, j] (bf16 [rows, ldl], as left by b2_lmhead_ce_fwd_keep; the pointer is
+ * row row0 of that matrix) becomes dlogits[r, j] = (exp(logit - lse[row0+r]) - [j == label]) * gscale_dev[0], 0 for
+ * ignored rows, bit-identical to what b2_lmhead_ce_bwd_dlogits writes; padding columns of the last 16-byte vector of a
+ * row are zeroed. HBM-bound (one read + one write of the matrix). labels and lse are the full arrays. Replaces the
+ * autograd backward of F.cross_entropy on the materialised logits ($SP/transformers/loss/loss_utils.py:28-42). */
+int b2_ce_dlogits_inplace(void* logits, long long ldl, const long long* labels, long long row0, long long rows, int V,
+                          int shift_T, long long ignore_index, const float* lse, const float* gscale_dev,
+                          b2_stream_t stream);
 /* Backward, step 1: recomputes the logits of rows [row0, row0+rows) and writes
  *   dlogits[r, j] = (exp(logit - lse[row0+r]) - [j == label]) * gscale_dev[0]   (bf16, [rows, ldd], ldd % 8 == 0;
  *   columns [V, ldd) are padding and are not written)

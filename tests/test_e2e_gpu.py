@@ -239,6 +239,39 @@ def test_full_size_lmhead_backward_vs_torch(b200):
     assert float(H.grad[ign].abs().max()) == 0.0
 
 
+def test_full_size_kept_logits_route_gives_the_recompute_route_bits(b200, monkeypatch):
+    """BASELINE configs[1] head shape through the public fused loss: keeping the forward's bf16 logits for the backward
+    (one chunk, the default) and recomputing them (B2_KEEP_LOGITS=0) produce the same loss, dH and dW bits."""
+    from b200_train import loss as L
+    N, D, V, T = 8192, 768, 50257, 1024
+    g = torch.Generator(device="cpu").manual_seed(5)
+    H0 = (torch.randn(N, D, generator=g) * 0.7).to(dev(), torch.bfloat16)
+    W0 = (torch.randn(V, D, generator=g) * 0.05).to(dev(), torch.bfloat16)
+    _, labels = TR.synthetic_hf_batch(N // T, T, V, seed=11, device=dev())
+    out = {}
+    for keep in (True, False):
+        monkeypatch.setattr(L, "_KEEP_LOGITS", keep)
+        H, W = H0.clone().requires_grad_(True), W0.clone().requires_grad_(True)
+        loss = b200.fused_lm_head_ce(H.view(N // T, T, D), W, labels)
+        (loss * 0.25).backward()                               # upstream gradient != 1 (gradient accumulation)
+        out[keep] = (loss.detach().clone(), H.grad.clone(), W.grad.clone())
+    assert torch.equal(out[True][0], out[False][0])
+    assert torch.equal(out[True][1].view(torch.int16), out[False][1].view(torch.int16)), "dH differs between the routes"
+    assert torch.equal(out[True][2].view(torch.int16), out[False][2].view(torch.int16)), "dW differs between the routes"
+    assert float(out[True][1].float().abs().max()) > 0
+    # no gradient wanted -> nothing is kept (evaluation must not pay for the logits buffer)
+    monkeypatch.setattr(L, "_KEEP_LOGITS", True)
+    with torch.no_grad():
+        ev = b200.fused_lm_head_ce(H0.view(N // T, T, D), W0, labels)
+    assert torch.equal(ev, out[True][0])
+    # the kept logits are consumed by the first backward: a second one over the same graph must say so
+    H, W = H0[:1024].clone().requires_grad_(True), W0.clone().requires_grad_(True)
+    loss = b200.fused_lm_head_ce(H.view(1, T, D), W, labels[:1])
+    loss.backward(retain_graph=True)
+    with pytest.raises(b200.B2Error):
+        loss.backward()
+
+
 def test_full_size_adamw_and_sumsq_properties(b200):
     from b200_train import ops
     n = (1 << 27) + 192

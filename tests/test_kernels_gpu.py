@@ -175,6 +175,49 @@ def test_lmhead_ce_bwd_dlogits_matches_oracle(ops, N, D, V, shift_T):
     assert (got[ign] == 0).all()
 
 
+@pytest.mark.parametrize("N,D,V", [(256, 128, 520), (300, 64, 283), (1024, 768, 5003)])
+@pytest.mark.parametrize("shift_T", [0, 10])
+@pytest.mark.parametrize("with_bias", [False, True])
+@pytest.mark.parametrize("gs", [0.37, -2.0])
+def test_lmhead_keep_logits_route_equals_recompute_route(ops, N, D, V, shift_T, with_bias, gs):
+    """Forward that keeps its bf16 logits + in-place transform == forward + recompute kernel, bit for bit; the kept
+    logits are the oracle's bf16 logits (to one bf16 ulp: the accumulation order inside the MMA differs)."""
+    if shift_T:
+        N = N // shift_T * shift_T
+    rng = np.random.default_rng(N + V + 7)
+    H, Ht = bf16_tensor(rng, (N, D))
+    W, Wt = bf16_tensor(rng, (V, D), scale=2.0 / np.sqrt(D))
+    b = (rng.standard_normal(V) * 0.1).astype(np.float32) if with_bias else None
+    bt = None if b is None else torch.from_numpy(b).to(dev())
+    y = make_labels(rng, N, V)
+    yt = torch.from_numpy(y).to(dev())
+    ldd = (V + 7) // 8 * 8
+    r0 = ops.lmhead_ce_fwd(Ht, Wt, yt, bias=bt, shift_T=shift_T)
+    kept = torch.full((N, ldd), float("nan"), dtype=torch.bfloat16, device=dev())
+    r1 = ops.lmhead_ce_fwd(Ht, Wt, yt, bias=bt, shift_T=shift_T, keep_logits=kept)
+    assert torch.equal(r0.loss, r1.loss) and torch.equal(r0.lse, r1.lse) and torch.equal(r0.n_valid, r1.n_valid)
+    o = O.lmhead_ce(H, W, y, bias=b, shift_T=shift_T, bf16_logits=True)
+    got = kept[:, :V].float().cpu().numpy()
+    assert np.isfinite(got).all()
+    assert (np.abs(got - o["logits"]) <= O.bf16_ulp(o["logits"])).all()
+    if ldd > V:
+        assert torch.isnan(kept[:, V:].float()).all()            # padding columns are not written by the forward
+    gscale = torch.tensor([gs], dtype=torch.float32, device=dev())
+    want = torch.full((N, ldd), float("nan"), dtype=torch.bfloat16, device=dev())
+    ops.lmhead_ce_bwd_dlogits(Ht, Wt, yt, r0.lse, gscale, 0, N, want, bias=bt, shift_T=shift_T)
+    # in place, in two row ranges to exercise row0
+    half = min(N, 128)
+    ops.ce_dlogits_inplace_(kept[:half], yt, r1.lse, gscale, 0, half, V, shift_T=shift_T)
+    if half < N:
+        ops.ce_dlogits_inplace_(kept[half:], yt, r1.lse, gscale, half, N - half, V, shift_T=shift_T)
+    assert torch.equal(kept[:, :V].view(torch.int16), want[:, :V].view(torch.int16))
+    if ldd > V:
+        assert (kept[:, V:] == 0).all()                           # ... and zeroed by the transform
+    # against the oracle's soft-max gradient of exactly these (kept) logits
+    d = O.cross_entropy_grad(got, o["labels"], gs)
+    assert (np.abs(kept[:, :V].float().cpu().numpy() - d) <= 2 * O.bf16_ulp(d) + 2e-6).all()
+
+
 # ------------------------------------------------------------------------------------------ CE over rows
 @pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
 @pytest.mark.parametrize("N,V", [(6, 11), (257, 283), (64, 5000)])

@@ -54,12 +54,19 @@ def main():
     r = ops.lmhead_ce_fwd(H, W, y, shift_T=T)
     res["fwd"] = timeit(lambda: ops.lmhead_ce_fwd(H, W, y, shift_T=T), args.iters, flush)
     res["bwd_dlogits(chunk)"] = timeit(lambda: ops.lmhead_ce_bwd_dlogits(H, W, y, r.lse, gs, 0, chunk, dl, shift_T=T), args.iters, flush)
+    if chunk == N:
+        res["fwd_keep_logits"] = timeit(lambda: ops.lmhead_ce_fwd(H, W, y, shift_T=T, keep_logits=dl), args.iters, flush)
+        res["dlogits_inplace"] = timeit(lambda: ops.ce_dlogits_inplace_(dl, y, r.lse, gs, 0, N, V, shift_T=T), args.iters, flush)
+        ops.lmhead_ce_bwd_dlogits(H, W, y, r.lse, gs, 0, chunk, dl, shift_T=T)          # real gradients for the GEMMs below
     res["gemm_dH(chunk)"] = timeit(lambda: ops.gemm_bf16(dl, W, dH[:chunk], chunk, D, V, b_mn_major=True), args.iters, flush)
     res["gemm_dW(chunk)"] = timeit(lambda: ops.gemm_bf16(dl, H[:chunk], dW, V, D, chunk, a_mn_major=True, b_mn_major=True), args.iters, flush)
     flops = 2.0 * chunk * V * D
     for k, ts in res.items():
-        n = N if k == "fwd" else chunk
+        n = N if k.startswith("fwd") else chunk
         ms = sorted(ts)[len(ts) // 2]
+        if k == "dlogits_inplace":
+            print(f"{k:22s} median {ms:8.3f} ms   {4.0 * n * V / ms / 1e6:8.1f} GB/s      all={['%.3f' % t for t in ts]}")
+            continue
         print(f"{k:22s} median {ms:8.3f} ms   {2.0 * n * V * D / ms / 1e9:8.1f} TFLOP/s   all={['%.3f' % t for t in ts]}")
     if args.plain:
         # fwd-shaped plain GEMM: logits[N, V] = H @ W^T (bf16 out) -- mainloop + the simplest epilogue
