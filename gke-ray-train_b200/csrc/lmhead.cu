@@ -252,23 +252,37 @@ umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
       for (int nb = nb0; nb < nb1; ++nb) {
         mbar_wait(&tfull_bar[as], aphase);
         tc_fence_after();
-#pragma unroll 1
-        for (int cc = 0; cc < BN / 64; ++cc) {
-          const int c = half * (BN / 64) + cc;       // 32-column chunk of the tile handled by this thread
-          const int col0 = nb * BN + c * 32;
-          if (!mode_stores(MODE) && col0 >= p.N) break;    // warp-uniform: nothing but padding from here on
+        // This warp's part of the tile: columns [colbase, colbase + 128) in 32-column chunks, of which the first nch hold
+        // real columns. The TMEM reads are software-pipelined: chunk cc+1 is requested before chunk cc is processed, and
+        // the accumulator stage goes back to the MMA thread as soon as the LAST chunk sits in registers — not after its
+        // arithmetic and stores — so the tensor pipe restarts on this buffer up to one chunk-time earlier.
+        const int colbase = nb * BN + half * (BN / 2);
+        int nch = (p.N - colbase + 31) / 32;
+        nch = nch < 0 ? 0 : (nch > BN / 64 ? BN / 64 : nch);
+        if (MODE == MODE_GEMM && p.c_dtype == 98) nch = 0;     // measurement aid (B2_DEBUG_NOEPI=2): not even the TMEM read
+        const uint32_t taddr0 = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(as * BN + half * (BN / 2));
+        bool released = false;
+        auto release = [&]() {                      // one arrival per warp hands the accumulator stage back to the MMA thread
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) {
+            if (PAIR) mbar_arrive_leader(&tempty_bar[as]); else mbar_arrive(&tempty_bar[as]);
+          }
+          released = true;
+        };
+        uint32_t ra[32], rb[32];
+        auto process = [&](const int cc, uint32_t (&r)[32], uint32_t (&rnext)[32]) {
+          const int col0 = colbase + cc * 32;
           if (mode_stores(MODE)) {
-            // d(logits) leaves through shared memory: each warp stages its own [32 rows x 32 columns] bf16 block (2 KiB,
+            // the tile leaves through shared memory: each warp stages its own [32 rows x 32 columns] bf16 block (2 KiB,
             // 64B-swizzled) and one lane hands it to the TMA engine (coalesced store, clipped at the matrix edge by the
             // tensor map). Two blocks per warp alternate; nothing here synchronises across warps.
-            if (col0 >= p.N) break;                  // warp-uniform: block entirely beyond the vocabulary
             if (lane == 0) bulk_wait_read_1();       // the store issued two blocks ago has drained its buffer
             __syncwarp();
           }
-          if (MODE == MODE_GEMM && p.c_dtype == 98) continue;   // measurement aid (B2_DEBUG_NOEPI=2): not even the TMEM read
-          uint32_t r[32];
-          tmem_ld_32x32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(as * BN + c * 32), r);
-          tmem_ld_wait();
+          tmem_ld_wait_regs(r);
+          if (cc + 1 < nch) tmem_ld_32x32(taddr0 + (uint32_t)((cc + 1) * 32), rnext);
+          else release();
 
           // storing modes: this thread's 32 values (one row of the warp's [32 x 32] block) -> 64B-swizzled staging box ->
           // one TMA store per warp
@@ -405,12 +419,14 @@ umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
               store_block(d);
             }
           }
+        };
+        if (nch > 0) tmem_ld_32x32(taddr0, ra);
+#pragma unroll 1
+        for (int cc = 0; cc < nch; cc += 2) {
+          process(cc, ra, rb);
+          if (cc + 1 < nch) process(cc + 1, rb, ra);
         }
-        tc_fence_before();
-        __syncwarp();
-        if (lane == 0) {                            // one arrival per warp hands the accumulator stage back to the MMA thread
-          if (PAIR) mbar_arrive_leader(&tempty_bar[as]); else mbar_arrive(&tempty_bar[as]);
-        }
+        if (!released) release();
         as ^= 1; if (as == 0) aphase ^= 1;
       }
 

@@ -127,7 +127,7 @@ int b2_lmhead_ce_fwd(const void* H, long long ldh, const void* W, long long ldw,
                      float* loss_out, long long* n_valid_out, int* err_out, b2_stream_t stream);
 /* Forward that also KEEPS the logits: as b2_lmhead_ce_fwd with round_logits_bf16 = 1, and additionally stores the
  * bf16-rounded logits (the values the loss was computed from) to logits_out [N, ldl] (ldl >= V, ldl % 8 == 0, 16-byte
- * aligned; columns [V, ldl) are padding and are not written). For callers that can afford N * ldl * 2 bytes between
+ * aligned; columns [V, ldl) are padding, unspecified afterwards). For callers that can afford N * ldl * 2 bytes between
  * forward and backward: the backward then needs no second pass over the tensor cores, see b2_ce_dlogits_inplace.
  * Same reference lines as b2_lmhead_ce_fwd — there the materialised tensor is `logits` itself
  * ($SP/transformers/models/llama/modeling_llama.py:486; fp32 copy at $SP/transformers/loss/loss_utils.py:57). */
@@ -145,7 +145,7 @@ int b2_ce_dlogits_inplace(void* logits, long long ldl, const long long* labels, 
                           b2_stream_t stream);
 /* Backward, step 1: recomputes the logits of rows [row0, row0+rows) and writes
  *   dlogits[r, j] = (exp(logit - lse[row0+r]) - [j == label]) * gscale_dev[0]   (bf16, [rows, ldd], ldd % 8 == 0;
- *   columns [V, ldd) are padding and are not written)
+ *   columns [V, ldd) are padding, unspecified afterwards)
  * H points at row row0 of the hidden states; labels and lse are the full arrays (indexed by row0 + r).
  * dH and dW then follow from two b2_gemm_bf16 calls on this chunk. */
 int b2_lmhead_ce_bwd_dlogits(const void* H, long long ldh, const void* W, long long ldw, const float* bias,

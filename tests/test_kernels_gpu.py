@@ -199,9 +199,9 @@ def test_lmhead_keep_logits_route_equals_recompute_route(ops, N, D, V, shift_T, 
     o = O.lmhead_ce(H, W, y, bias=b, shift_T=shift_T, bf16_logits=True)
     got = kept[:, :V].float().cpu().numpy()
     assert np.isfinite(got).all()
-    assert (np.abs(got - o["logits"]) <= O.bf16_ulp(o["logits"])).all()
-    if ldd > V:
-        assert torch.isnan(kept[:, V:].float()).all()            # padding columns are not written by the forward
+    # one bf16 ulp, plus the fp32 accumulation-order difference that shows when a logit is close to zero
+    assert (np.abs(got - o["logits"]) <= O.bf16_ulp(o["logits"]) + 5e-5).all()
+    # (the padding columns [V, ldd) are unspecified after the forward: the TMA store clips in 16-byte units)
     gscale = torch.tensor([gs], dtype=torch.float32, device=dev())
     want = torch.full((N, ldd), float("nan"), dtype=torch.bfloat16, device=dev())
     ops.lmhead_ce_bwd_dlogits(Ht, Wt, yt, r0.lse, gscale, 0, N, want, bias=bt, shift_T=shift_T)
