@@ -77,6 +77,7 @@ struct Params {
   const float* bias; int round_bf16;
   float2* part; long long part_stride; float* zt;
   const float* lse; const float* gscale; __nv_bfloat16* dlogits; long long ldd;
+  int store_wide;                    // storing modes: 1 = one [32 x 64] TMA store per two chunks, 0 = one [32 x 32] per chunk
 };
 
 __device__ __forceinline__ long long label_at(const Params& p, long long i) {
@@ -277,8 +278,16 @@ umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
             // the tile leaves through shared memory: each warp stages its own [32 rows x 32 columns] bf16 block (2 KiB,
             // 64B-swizzled) and one lane hands it to the TMA engine (coalesced store, clipped at the matrix edge by the
             // tensor map). Two blocks per warp alternate; nothing here synchronises across warps.
-            if (lane == 0) bulk_wait_read_1();       // the store issued two blocks ago has drained its buffer
-            __syncwarp();
+            // (store_wide: one [32 x 64] block, 4 KiB, 128B-swizzled, filled by two consecutive chunks and stored once.)
+            if (p.store_wide) {
+              if ((cc & 1) == 0) {
+                if (lane == 0) bulk_wait_read_all();   // this warp's previous store has drained the block
+                __syncwarp();
+              }
+            } else {
+              if (lane == 0) bulk_wait_read_1();     // the store issued two blocks ago has drained its buffer
+              __syncwarp();
+            }
           }
           tmem_ld_wait_regs(r);
           if (cc + 1 < nch) tmem_ld_32x32(taddr0 + (uint32_t)((cc + 1) * 32), rnext);
@@ -290,6 +299,23 @@ umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
             uint32_t w[16];
 #pragma unroll
             for (int j = 0; j < 32; j += 2) w[j >> 1] = pack_bf16(v[j], v[j + 1]);
+            if (p.store_wide) {
+              uint8_t* box = smem + STAGES * STAGE_BYTES + (warp - 4) * (32 * 128);
+              uint8_t* rowp = box + lane * 128;
+              const int h = cc & 1;                  // which 64-byte half of the 128-byte row this chunk fills
+#pragma unroll
+              for (int k = 0; k < 4; ++k)             // 16-byte chunk 4h+k of the row, SWIZZLE_128B: index ^ (row & 7)
+                st_shared_v4(rowp + (((4 * h + k) ^ (lane & 7)) << 4), w[4 * k], w[4 * k + 1], w[4 * k + 2], w[4 * k + 3]);
+              if (h == 1 || cc + 1 == nch) {         // block complete (a lone first half: the rest lies beyond the matrix edge)
+                fence_proxy_async_smem();
+                __syncwarp();
+                if (lane == 0) {
+                  tma_store_2d_hint(&tmD, box, colbase + (cc >> 1) * 64, m0 + q * 32, store_policy);
+                  bulk_commit();
+                }
+              }
+              return;
+            }
             uint8_t* box = smem + STAGES * STAGE_BYTES + ((warp - 4) * 2 + (int)(store_seq & 1)) * (32 * 64);
             uint8_t* rowp = box + lane * 64;
 #pragma unroll
@@ -597,6 +623,16 @@ int num_sms() {
   return n;
 }
 
+// Shape of the TMA stores of the storing epilogues: [32 x 64] (one per two chunks; default) or [32 x 32] (B2_STORE_BOX=32)
+bool store_wide() {
+  static const bool wide = [] { const char* e = getenv("B2_STORE_BOX"); return e == nullptr ? true : atoi(e) == 64; }();
+  return wide;
+}
+int make_store_tmap(CUtensorMap* m, const void* ptr, long long cols, long long rows, long long pitch, const char* what) {
+  return store_wide() ? make_tmap(m, ptr, cols, rows, pitch, 64, 32, what, CU_TENSOR_MAP_SWIZZLE_128B)
+                      : make_tmap(m, ptr, cols, rows, pitch, 32, 32, what, CU_TENSOR_MAP_SWIZZLE_64B);
+}
+
 // CTA pairs (tcgen05 cta_group::2, M = 256 per MMA) for the plain GEMMs (long K, light epilogue); the two cross-entropy
 // kernels, whose epilogues are the heavier side, measured faster with independent CTAs that are not coupled through a
 // shared accumulator hand-off (profiles/README.md). B2_PAIR=0 / B2_PAIR=1 in the environment forces one shape
@@ -775,7 +811,8 @@ static int lmhead_ce_fwd_impl(const void* H, long long ldh, const void* W, long 
       if ((rc = launch<MODE_CE_FWD, 0, 0>(ta, tb, ta, p, stream)) != B2_OK) return rc;
     } else {
       CUtensorMap td;
-      if ((rc = make_tmap(&td, logits_out, V, N, ldl, 32, 32, "b2_lmhead_ce_fwd_keep logits", CU_TENSOR_MAP_SWIZZLE_64B)) != B2_OK) return rc;
+      if ((rc = make_store_tmap(&td, logits_out, V, N, ldl, "b2_lmhead_ce_fwd_keep logits")) != B2_OK) return rc;
+      p.store_wide = store_wide();
       if ((rc = launch<MODE_CE_FWD_KEEP, 0, 0>(ta, tb, td, p, stream)) != B2_OK) return rc;
     }
     ce_combine_kernel<<<(unsigned)((N + 255) / 256), 256, 0, stream>>>(p.part, p.part_stride, 2 * p.n_splits, N, lse);
@@ -845,6 +882,7 @@ extern "C" int b2_lmhead_ce_bwd_dlogits(const void* H, long long ldh, const void
   p.bias = bias; p.round_bf16 = round_logits_bf16;
   p.lse = lse; p.gscale = gscale_dev; p.dlogits = static_cast<__nv_bfloat16*>(dlogits); p.ldd = ldd;
   CUtensorMap td;
-  if ((rc = make_tmap(&td, dlogits, V, rows, ldd, 32, 32, "b2_lmhead_ce_bwd_dlogits dlogits", CU_TENSOR_MAP_SWIZZLE_64B)) != B2_OK) return rc;
+  if ((rc = make_store_tmap(&td, dlogits, V, rows, ldd, "b2_lmhead_ce_bwd_dlogits dlogits")) != B2_OK) return rc;
+  p.store_wide = store_wide();
   return launch<MODE_CE_BWD, 0, 0>(ta, tb, td, p, stream);
 }
