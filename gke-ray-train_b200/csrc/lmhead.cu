@@ -11,10 +11,13 @@
 // Backward recomputes the tile and writes d(logits) for a bounded chunk of rows only (bf16), which two
 // plain GEMMs (same mainloop, MODE_GEMM) turn into dH and dW.
 //
-// One kernel template, three epilogues:
-//   MODE_GEMM    C[M,N] (+)= A[M,K] * B[N,K]^T          (A/B each K-major or MN-major in memory)
-//   MODE_CE_FWD  per (row, vocab split): (max, sumexp) partials + label logit
-//   MODE_CE_BWD  dlogits[row, col] = (exp(logit - lse[row]) - [col == label]) * gscale   (0 for ignored rows)
+// One kernel template, four epilogues:
+//   MODE_GEMM         C[M,N] (+)= A[M,K] * B[N,K]^T          (A/B each K-major or MN-major in memory)
+//   MODE_CE_FWD       per (row, vocab split): (max, sumexp) partials + label logit
+//   MODE_CE_BWD       dlogits[row, col] = (exp(logit - lse[row]) - [col == label]) * gscale   (0 for ignored rows)
+//   MODE_CE_FWD_KEEP  MODE_CE_FWD that also stores the bf16-rounded logits; ce_dlogits_inplace_kernel then turns them
+//                     into dlogits in place (HBM-bound), so the backward needs no MODE_CE_BWD pass. Used when the caller
+//                     can hold [rows, V] bf16 between forward and backward (b200_train/loss.py: one chunk of rows).
 //
 // Tile 128 (M) x 256 (N) x 64 (K) per CTA, tcgen05.mma kind::f16 (bf16 in, fp32 out), fp32 accumulators double-buffered
 // in TMEM (2 x 256 columns) so the epilogue of tile i overlaps the MMAs of tile i+1. Two shapes of the same template:
@@ -23,7 +26,7 @@
 //                6-stage 32 KiB ring; the leader issues the MMAs and multicasts the commits)
 // Warp roles (384 threads, 1 CTA/SM, persistent over work units): warp 0 = TMA producer, warp 1 = MMA issuer (one thread),
 // warp 2 = TMEM allocator, warps 4-11 = epilogue (warp w owns TMEM lane quarter w%4 and one 128-column half; one thread =
-// one row). The dlogits epilogue leaves through 64B-swizzled shared memory and TMA stores, one 32x32 block per warp.
+// one row). The storing epilogues leave through 128B-swizzled shared memory and TMA stores, one 32x64 block per warp.
 // Tensor-bound: algorithmic flops = 2*M*N*K per pass (measurements in profiles/README.md).
 #include "b2_common.cuh"
 #include "umma.cuh"
