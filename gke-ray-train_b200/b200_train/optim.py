@@ -132,6 +132,14 @@ class AdamW(torch.optim.Optimizer):
             self._setup()
         return self._buffers
 
+    def add_param_group(self, param_group):
+        """Allowed until the flat buffers exist (the constructor goes through here); afterwards the layout of parameters,
+        gradients and state is fixed, and a group added later would silently never be updated."""
+        if getattr(self, "_buffers", None) is not None:
+            raise B2Error("b200_train.AdamW: add_param_group() after the parameters were flattened is not supported; "
+                          "pass every param_group to the constructor")
+        return super().add_param_group(param_group)
+
     # ------------------------------------------------------------------ torch.optim.Optimizer surface
     def zero_grad(self, set_to_none=True):
         """ref :273 calls zero_grad(set_to_none=True). The gradients live in a persistent flat buffer that the

@@ -77,6 +77,9 @@ def test_adamw_bookkeeping_matches_torch_layout():
         b200_train.AdamW(m.parameters(), amsgrad=True)
     with pytest.raises(ValueError):
         b200_train.AdamW(m.parameters(), lr=-1.0)
+    # once the flat layout exists a late group would never be updated: refused rather than ignored
+    with pytest.raises(b200_train.B2Error):
+        opt.add_param_group({"params": [nn.Parameter(torch.zeros(3))]})
 
 
 def test_loss_modules_refuse_cpu_tensors():
