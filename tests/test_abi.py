@@ -88,3 +88,36 @@ def test_no_cpu_fallback(lib):
         ops.sumsq(x)
     with pytest.raises(lib.B2Error):
         ops.adamw_(x, x, x.clone(), x.clone(), lr=1e-3, step=1)
+
+
+def test_new_f1_entry_points_reject_bad_arguments(lib):
+    L = lib.lib
+    # kept-logits forward: the logits buffer must exist, be 16-byte aligned, with a row pitch >= V that is a multiple of 8
+    assert L.b2_lmhead_ce_fwd_keep(16, 8, 16, 8, None, 16, 10, 8, 8, 0, -100, 16, 0, 16, 16, 16, 16, None, None, 8, None) == -1
+    assert b"null logits" in L.b2_last_error()
+    assert L.b2_lmhead_ce_fwd_keep(16, 8, 16, 8, None, 16, 10, 8, 8, 0, -100, 16, 0, 16, 16, 16, 16, None, 16, 9, None) == -1
+    assert b"ldl" in L.b2_last_error()
+    assert L.b2_ce_dlogits_inplace(16, 12, 16, 0, 4, 10, 0, -100, 16, 16, None) == -1
+    assert b"ldl" in L.b2_last_error()
+    assert L.b2_ce_dlogits_inplace(None, 16, 16, 0, 4, 10, 0, -100, 16, 16, None) == -1
+    assert L.b2_ce_dlogits_inplace(16, 16, 16, 0, 0, 10, 0, -100, 16, 16, None) == 0       # zero rows: nothing to do
+
+
+def test_built_kernels_target_sm100a_use_the_tensor_path_and_do_not_spill():
+    """Static check on the shipped library (cuobjdump, no GPU): every kernel is sm_100a code without local-memory
+    spills, and the F1 kernels really contain the tcgen05 / TMA instructions (a silent fallback to mma.sync-era code
+    would not)."""
+    import shutil
+    import subprocess
+    from b200_train import _lib
+    if shutil.which("cuobjdump") is None:
+        pytest.skip("cuobjdump not on PATH")
+    res = subprocess.run(["cuobjdump", "-res-usage", _lib.LIB_PATH], capture_output=True, text=True, check=True).stdout
+    assert "sm_100a" in res and not re.search(r"arch = sm_(?!100a)", res)
+    usage = re.findall(r"Function (\S+):\s*\n\s*REG:(\d+) STACK:(\d+) SHARED:(\d+) LOCAL:(\d+)", res)
+    assert len(usage) >= 40
+    assert all(int(local) == 0 for _, _, _, _, local in usage), [n for n, *_r, loc in usage if int(loc)]
+    assert all(int(reg) <= 168 for n, reg, *_ in usage if "umma_kernel" in n)      # 384 threads x 168 = the register file
+    sass = subprocess.run(["cuobjdump", "-sass", _lib.LIB_PATH], capture_output=True, text=True, check=True).stdout
+    for mnemonic in ("UTCHMMA", "UTCBAR", "LDTM", "UTMALDG", "UTMASTG", "LDGMC"):
+        assert mnemonic in sass, f"{mnemonic} missing from the built library"
