@@ -159,7 +159,8 @@ class _LMHeadCEFn(torch.autograd.Function):
 
 def fused_lm_head_ce(hidden, weight, labels, bias=None, *, shift=True, ignore_index=-100, reduction="mean",
                      num_items_in_batch=None, round_logits_bf16=True, chunk_rows=DEFAULT_CHUNK_ROWS, check_labels=False):
-    """loss = CE(hidden @ weight.T (+bias), labels) without materialising the logits.
+    """loss = CE(hidden @ weight.T (+bias), labels) without the fp32 [N, V] logits / log-probability tensors of the stock path
+    (at most a bf16 copy of the logits lives from this forward to its backward, see _KEEP_LOGITS above).
 
     hidden [..., T, D] bf16, weight [V, D] bf16, labels [..., T] int64. shift=True applies the causal shift inside
     (row t is scored against labels[t+1], the last position ignored) exactly as HF's ForCausalLMLoss; shift=False

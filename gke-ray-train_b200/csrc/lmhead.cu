@@ -6,7 +6,7 @@
 //                                              BasicLLM.fc_out, ref: ray-jobs/pytorch_llm_ray.py:87,104)
 //   loss   = ForCausalLMLoss(logits, labels)  (transformers/loss/loss_utils.py:45-67: .float(), shift, CE with
 //                                              ignore_index=-100; nn.CrossEntropyLoss at ref: pytorch_llm_ray.py:237,275)
-// The [tokens x vocab] logits are never written to memory: each 128x256 logits tile lives in TMEM, and
+// The fp32 [tokens x vocab] logits are never written to memory: each 128x256 logits tile lives in TMEM, and
 // the epilogue warps fold it into a per-row running (max, sum-exp) and pick out the label's logit.
 // Backward recomputes the tile and writes d(logits) for a bounded chunk of rows only (bf16), which two
 // plain GEMMs (same mainloop, MODE_GEMM) turn into dH and dW.

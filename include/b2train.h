@@ -113,7 +113,9 @@ int b2_ce_rows_bwd(const void* logits, int dtype, long long N, long long V, long
  * Replaces lm_head(hidden) followed by the causal-LM loss — ref: ray-jobs/fine_tune_llama_ray.py:333
  * (trainer.train() -> $SP/transformers/models/llama/modeling_llama.py:486-491 ->
  * $SP/transformers/loss/loss_utils.py:45-67) and BasicLLM.fc_out + criterion, ref:
- * ray-jobs/pytorch_llm_ray.py:87,104,237,275. The [N, V] logits are never written to memory.
+ * ray-jobs/pytorch_llm_ray.py:87,104,237,275. b2_lmhead_ce_fwd never writes the [N, V] logits to
+ * memory (b2_lmhead_ce_fwd_keep optionally leaves a bf16 copy for the backward; the fp32 [N, V] tensors of the reference
+ * never exist).
  * H: [N, ldh] bf16 hidden states (D used columns); W: [V, ldw] bf16 (nn.Linear weight layout);
  * bias: fp32 [V] or NULL. ldh, ldw multiples of 8.
  * round_logits_bf16 != 0 rounds each logit to bf16 before the soft-max, which is what the reference's
