@@ -121,3 +121,35 @@ def test_built_kernels_target_sm100a_use_the_tensor_path_and_do_not_spill():
     sass = subprocess.run(["cuobjdump", "-sass", _lib.LIB_PATH], capture_output=True, text=True, check=True).stdout
     for mnemonic in ("UTCHMMA", "UTCBAR", "LDTM", "UTMALDG", "UTMASTG", "LDGMC"):
         assert mnemonic in sass, f"{mnemonic} missing from the built library"
+
+
+def test_more_entry_points_reject_bad_arguments(lib):
+    L = lib.lib
+    assert L.b2_gemm_bf16(16, 0, 8, 16, 0, 8, 16, 1, 8, 0, 8, 8, 0, None, 0, None) == -1          # M = 0
+    assert b"bad shape" in L.b2_last_error()
+    assert L.b2_gemm_bf16(16, 0, 8, 16, 0, 8, 16, 5, 8, 8, 8, 8, 0, None, 0, None) == -1          # c_dtype
+    assert L.b2_gemm_bf16(16, 0, 8, 16, 0, 8, 16, 1, 4, 8, 8, 8, 0, None, 0, None) == -1          # ldc < N
+    assert L.b2_gather_windows(None, 10, None, 2, 4, None, None, None, None) == -1
+    assert b"null" in L.b2_last_error()
+    assert L.b2_gather_windows(16, 0, 16, 2, 4, 16, 16, None, None) == -1                          # no tokens
+    assert L.b2_gather_windows(None, 0, None, 0, 4, None, None, None, None) == 0                   # empty batch: nothing to do
+    assert L.b2_peer_allgather(None, None, 2, 0, 0, 12, 1, 1, None) == -1                          # 12 bf16 != k * 16 bytes
+    assert b"16 bytes" in L.b2_last_error()
+    assert L.b2_peer_allgather(None, None, 2, 5, 0, 16, 1, 1, None) == -1
+    assert L.b2_symm_alloc(0, None, None) == -1
+    assert L.b2_lmhead_ce_bwd_dlogits(16, 8, 16, 8, None, 16, 0, 4, 8, 10, 0, -100, 1, 16, 16, 16, 12, None) == -1   # ldd % 8
+    assert b"ldd" in L.b2_last_error()
+
+
+def test_without_a_gpu_device_calls_fail_loudly(lib):
+    """No CPU path anywhere: where there is no device, anything that would touch one returns an error code and a message
+    (this test only runs where CUDA is absent, e.g. the build container)."""
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("a GPU is present")
+    L = lib.lib
+    p = ctypes.c_void_p()
+    h = (ctypes.c_ubyte * 64)()
+    rc = L.b2_symm_alloc(4096, ctypes.byref(p), h)
+    assert rc == -2 and L.b2_last_error()                                   # B2_ERR_CUDA, with the driver's reason
+    assert L.b2_device_count() <= 0
