@@ -4,7 +4,9 @@ ref: ray-jobs/pytorch_llm_ray.py:12-16 imports `ray.train`, `ScalingConfig`, `Ru
 `TorchTrainer`, `TorchConfig`; it calls `train.get_context()` (:125), `train.torch.get_device()` (:128),
 `train.torch.prepare_data_loader` (:216), `train.torch.prepare_model` (:230), `train.report` (:310),
 `train.CheckpointConfig` (:355) and `TorchTrainer(...).fit()` (:368-376). ref: ray-jobs/fine_tune_llama_ray.py:445-457
-does the same with `ScalingConfig(num_workers, use_gpu=True, resources_per_worker={"GPU": 1})`.
+does the same with `ScalingConfig(num_workers, use_gpu=True, resources_per_worker={"GPU": 1})`, reads
+`get_context().get_world_rank()/get_world_size()` (:201-202) and imports `RayTrainReportCallback`, `prepare_trainer` from
+`ray.train.huggingface.transformers` (:8) — here `train.huggingface.transformers`.
 
 A job written against Ray switches with
     from b200_train import train
@@ -203,6 +205,53 @@ def prepare_data_loader(data_loader, add_dist_sampler=True, move_to_device=True,
 # `train.torch.*` namespace, as in `from ray import train; train.torch.prepare_model(model)`
 torch = types.SimpleNamespace(prepare_model=_ddp.prepare_model, prepare_data_loader=prepare_data_loader,
                               get_device=_ddp.get_device)
+
+
+def _prepare_trainer(trainer):
+    """`ray.train.huggingface.transformers.prepare_trainer(trainer)` (imported at ref: fine_tune_llama_ray.py:8): Ray's
+    version validates the trainer's callbacks and swaps its data loaders for Ray Data ones when Ray Datasets are passed; the
+    reference passes HF datasets, so the trainer comes back unchanged."""
+    return trainer
+
+
+def _make_report_callback():
+    """`RayTrainReportCallback` (ref: fine_tune_llama_ray.py:8): a transformers TrainerCallback that forwards the
+    Trainer's logs, and the checkpoint it just saved, to `train.report`. Built lazily: transformers is only needed by
+    jobs that use it."""
+    from transformers.trainer_callback import TrainerCallback
+
+    class RayTrainReportCallback(TrainerCallback):
+        CHECKPOINT_NAME = "checkpoint"
+
+        def __init__(self):
+            self.metrics = {}
+
+        def on_log(self, args, state, control, logs=None, **kwargs):
+            self.metrics.update(logs or {})
+
+        def on_save(self, args, state, control, **kwargs):
+            ckpt_dir = os.path.join(args.output_dir, f"checkpoint-{state.global_step}")
+            ckpt = None
+            if os.path.isdir(ckpt_dir):
+                tmp = tempfile.mkdtemp()
+                shutil.copytree(ckpt_dir, os.path.join(tmp, self.CHECKPOINT_NAME))
+                ckpt = Checkpoint.from_directory(tmp)
+            report({**self.metrics, "step": state.global_step, "epoch": state.epoch}, checkpoint=ckpt)
+
+    return RayTrainReportCallback
+
+
+class _HFTransformersNS(types.SimpleNamespace):
+    def __getattr__(self, name):
+        if name == "RayTrainReportCallback":
+            cls = _make_report_callback()
+            setattr(self, name, cls)
+            return cls
+        raise AttributeError(name)
+
+
+# `train.huggingface.transformers.*`, as in `from ray.train.huggingface.transformers import RayTrainReportCallback, prepare_trainer`
+huggingface = types.SimpleNamespace(transformers=_HFTransformersNS(prepare_trainer=_prepare_trainer))
 
 
 def _free_port():

@@ -206,3 +206,33 @@ def test_comm_hook_state_refuses_to_exist_without_group_or_gpu():
     assert list(sig.parameters) == ["state", "bucket"]
     assert all(p.annotation is inspect.Parameter.empty for p in sig.parameters.values())
     assert sig.return_annotation is inspect.Signature.empty
+
+
+def test_hf_report_callback_and_prepare_trainer(tmp_path):
+    """`from ray.train.huggingface.transformers import RayTrainReportCallback, prepare_trainer`
+    (ref: ray-jobs/fine_tune_llama_ray.py:8) has a counterpart under b200_train.train; the callback forwards the HF
+    Trainer's logs and the checkpoint it just saved to train.report (driven by hand here: a real Trainer needs accelerate,
+    which is not installed)."""
+    from types import SimpleNamespace
+    from b200_train import train
+    hf = train.huggingface.transformers
+    sentinel = object()
+    assert hf.prepare_trainer(sentinel) is sentinel
+    cb = hf.RayTrainReportCallback()
+    assert hf.RayTrainReportCallback is type(cb)                    # built once, then cached on the namespace
+    out = tmp_path / "out"
+    (out / "checkpoint-7").mkdir(parents=True)
+    (out / "checkpoint-7" / "weights.bin").write_bytes(b"abc")
+    store = tmp_path / "store"
+    store.mkdir()
+    old = train._ctx
+    train._ctx = train._Context(0, 1, 0, str(store), train.CheckpointConfig(num_to_keep=1))
+    try:
+        args, state = SimpleNamespace(output_dir=str(out)), SimpleNamespace(global_step=7, epoch=0.5)
+        cb.on_log(args, state, None, logs={"loss": 1.25})
+        cb.on_save(args, state, None)
+        rep = train._ctx.reports[-1]
+        assert rep["loss"] == 1.25 and rep["step"] == 7
+        assert os.path.isfile(os.path.join(rep["_checkpoint_path"], "checkpoint", "weights.bin"))
+    finally:
+        train._ctx = old
