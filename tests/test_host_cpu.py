@@ -236,3 +236,26 @@ def test_hf_report_callback_and_prepare_trainer(tmp_path):
         assert os.path.isfile(os.path.join(rep["_checkpoint_path"], "checkpoint", "weights.bin"))
     finally:
         train._ctx = old
+
+
+def test_hf_cosine_schedule_drives_our_param_groups_like_torchs():
+    """ref: ray-jobs/fine_tune_config.json:18,20 — `cosine` schedule, warm-up ratio 0.03, built by HF on top of the
+    optimizer's param_groups. The schedule must see (and mutate) ours exactly as it does torch.optim.AdamW's."""
+    from transformers import get_scheduler
+    import b200_train
+    steps, warm = 200, int(0.03 * 200)
+    lrs = {}
+    for name, cls in (("ours", b200_train.AdamW), ("torch", torch.optim.AdamW)):
+        m = nn.Linear(4, 4)
+        opt = cls([{"params": [m.weight], "weight_decay": 1e-3}, {"params": [m.bias], "weight_decay": 0.0}], lr=2e-4)
+        sched = get_scheduler("cosine", optimizer=opt, num_warmup_steps=warm, num_training_steps=steps)
+        seq = []
+        import warnings
+        with warnings.catch_warnings():
+            warnings.simplefilter("ignore")      # "scheduler before optimizer": no optimizer arithmetic happens in this test
+            for _ in range(steps):
+                seq.append([g["lr"] for g in opt.param_groups])
+                sched.step()
+        lrs[name] = seq
+    assert lrs["ours"] == lrs["torch"]
+    assert lrs["ours"][0] == [0.0, 0.0] and max(v[0] for v in lrs["ours"]) == pytest.approx(2e-4)
