@@ -8,7 +8,8 @@ import os
 from ctypes import c_char_p, c_double, c_float, c_int, c_longlong, c_size_t, c_void_p
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libb2train.so")
+# B2_LIB: load another build of the same library (A/B measurements of a kernel change); default is the in-tree build
+LIB_PATH = os.environ.get("B2_LIB") or os.path.join(_HERE, "libb2train.so")
 
 F32, BF16 = 0, 1
 

@@ -272,6 +272,47 @@ def test_full_size_kept_logits_route_gives_the_recompute_route_bits(b200, monkey
         loss.backward()
 
 
+@pytest.mark.parametrize("D", [2048, 4096])
+def test_llama_head_shapes_match_torch_and_routes_agree(b200, monkeypatch, D):
+    """BASELINE configs[2] / configs[3] head shapes (ref: ray-jobs/fine_tune_llama_ray.py:230-241,333 loads a 128 256-word
+    vocabulary): N = 2 x 2048 tokens, D = 2048 (Llama-3.2-1B) and 4096 (Llama-3-8B; 64 K-blocks, the dH GEMM takes the
+    split-K schedule). Loss and token count against torch's cross_entropy on (H @ W^T).float(); dH / dW relative Frobenius
+    error < 1e-2 against autograd; ignored rows exactly zero; kept-logits route and recompute route give the same bits."""
+    from b200_train import loss as L
+    from b200_train import ops
+    N, V, T = 4096, 128256, 2048
+    g = torch.Generator(device="cpu").manual_seed(40 + D)
+    H0 = (torch.randn(N, D, generator=g) * 0.7).to(dev(), torch.bfloat16)
+    W0 = (torch.randn(V, D, generator=g) * (0.8 / D ** 0.5)).to(dev(), torch.bfloat16)
+    _, labels = TR.synthetic_hf_batch(N // T, T, V, seed=12, device=dev())
+    ys = torch.full_like(labels, -100); ys[:, :-1] = labels[:, 1:]
+    # reference: the stock arithmetic on the same device
+    Hr, Wr = H0.clone().requires_grad_(True), W0.clone().requires_grad_(True)
+    want = torch.nn.functional.cross_entropy((Hr @ Wr.t()).float(), ys.reshape(-1), ignore_index=-100)
+    (want * 0.25).backward()
+    r = ops.lmhead_ce_fwd(H0, W0, labels.reshape(-1), shift_T=T)
+    assert int(r.n_valid.item()) == int((ys != -100).sum())           # bit-exact token count
+    assert int(r.err.item()) == 0
+    out = {}
+    for keep in (True, False):
+        monkeypatch.setattr(L, "_KEEP_LOGITS", keep)
+        H, W = H0.clone().requires_grad_(True), W0.clone().requires_grad_(True)
+        loss = b200.fused_lm_head_ce(H.view(N // T, T, D), W, labels)
+        (loss * 0.25).backward()
+        out[keep] = (loss.detach().clone(), H.grad.clone(), W.grad.clone())
+        del H, W
+    np.testing.assert_allclose(float(out[True][0]), float(want), rtol=0, atol=2e-3)
+    assert torch.equal(out[True][0], out[False][0])
+    assert torch.equal(out[True][1].view(torch.int16), out[False][1].view(torch.int16)), "dH differs between the routes"
+    assert torch.equal(out[True][2].view(torch.int16), out[False][2].view(torch.int16)), "dW differs between the routes"
+    for got, ref, name in ((out[True][1], Hr.grad, "dH"), (out[True][2], Wr.grad, "dW")):
+        got, ref = got.float(), ref.float()
+        rel = (got - ref).norm() / ref.norm()
+        assert torch.isfinite(got).all() and rel < 1e-2, f"{name}: relative Frobenius error {rel:.3e}"
+    ign = ys.reshape(-1) == -100
+    assert ign.any() and float(out[True][1][ign].abs().max()) == 0.0
+
+
 def test_full_size_adamw_and_sumsq_properties(b200):
     from b200_train import ops
     n = (1 << 27) + 192
