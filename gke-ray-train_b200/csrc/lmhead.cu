@@ -153,7 +153,9 @@ umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
 
   if (warp == 0) {
     // ------------------------------------------------------------ TMA producer
-    if (lane == 0) {
+    {
+      // the whole warp runs the loops; one elected lane issues the expect_tx and the TMA loads (see umma::elect_one)
+      const bool issuer = elect_one();
       int stage = 0; uint32_t phase = 0;
       for (int u = cid; u < num_units; u += ncl) {
         const Unit t = decode_unit(p, u);
@@ -162,6 +164,7 @@ umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
           const int n0 = nb * BN + crank * BN_CTA;    // first column of B this CTA loads
           for (int kb = t.kb0; kb < t.kb1; ++kb) {
             mbar_wait(&empty_bar[stage], phase ^ 1);
+            if (!issuer) { if (++stage == STAGES) { stage = 0; phase ^= 1; } continue; }
             if (crank == 0) mbar_arrive_expect_tx(&full_bar[stage], NC * STAGE_BYTES);
             uint8_t* sa = smem + stage * STAGE_BYTES;
             uint8_t* sb = sa + A_STAGE_BYTES;
@@ -185,7 +188,9 @@ umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
     }
   } else if (warp == 1) {
     // ------------------------------------------------------------ MMA issuer (one thread)
-    if (lane == 0 && crank == 0) {
+    if (crank == 0) {
+      // the whole warp runs the loops (warp-uniform control flow); one elected lane issues the MMAs and commits
+      const bool issuer = elect_one();
       constexpr uint32_t idesc = make_idesc_bf16(BM * NC, BN, A_MN, B_MN);
       int stage = 0; uint32_t phase = 0;
       int as = 0; uint32_t aphase = 0;
@@ -204,19 +209,21 @@ umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
             // descriptors differ from the stage-0 / k-0 ones only in the 14-bit start-address field (16-byte units)
             const uint64_t adesc_s = adesc0 + (uint64_t)((uint32_t)(stage * STAGE_BYTES) >> 4);
             const uint64_t bdesc_s = bdesc0 + (uint64_t)((uint32_t)(stage * STAGE_BYTES) >> 4);
+            if (issuer) {
 #pragma unroll
-            for (int k = 0; k < BK / UK; ++k) {
-              const uint64_t adesc = adesc_s + (uint64_t)((A_MN ? k * (UK * 128) : k * (UK * 2)) >> 4);
-              const uint64_t bdesc = bdesc_s + (uint64_t)((B_MN ? k * (UK * 128) : k * (UK * 2)) >> 4);
-              if (PAIR) mma_bf16_ss_pair(tmem_d, adesc, bdesc, idesc, (uint32_t)(kb > t.kb0 || k > 0));
-              else mma_bf16_ss(tmem_d, adesc, bdesc, idesc, (uint32_t)(kb > t.kb0 || k > 0));
+              for (int k = 0; k < BK / UK; ++k) {
+                const uint64_t adesc = adesc_s + (uint64_t)((A_MN ? k * (UK * 128) : k * (UK * 2)) >> 4);
+                const uint64_t bdesc = bdesc_s + (uint64_t)((B_MN ? k * (UK * 128) : k * (UK * 2)) >> 4);
+                if (PAIR) mma_bf16_ss_pair(tmem_d, adesc, bdesc, idesc, (uint32_t)(kb > t.kb0 || k > 0));
+                else mma_bf16_ss(tmem_d, adesc, bdesc, idesc, (uint32_t)(kb > t.kb0 || k > 0));
+              }
+              // frees the smem slot (in both CTAs of a pair) once these MMAs retire
+              if (PAIR) mma_commit_pair(&empty_bar[stage]); else mma_commit(&empty_bar[stage]);
             }
-            // frees the smem slot (in both CTAs of a pair) once these MMAs retire
-            if (PAIR) mma_commit_pair(&empty_bar[stage]); else mma_commit(&empty_bar[stage]);
             if (++stage == STAGES) { stage = 0; phase ^= 1; }
           }
           // accumulator tile complete (each CTA of a pair reads its own 128 rows from its own TMEM)
-          if (PAIR) mma_commit_pair(&tfull_bar[as]); else mma_commit(&tfull_bar[as]);
+          if (issuer) { if (PAIR) mma_commit_pair(&tfull_bar[as]); else mma_commit(&tfull_bar[as]); }
           as ^= 1; if (as == 0) aphase ^= 1;
         }
       }
@@ -230,6 +237,7 @@ umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
     const int trow = q * 32 + lane;                 // row inside the tile
     int as = 0; uint32_t aphase = 0;
     uint32_t store_seq = 0;                         // storing modes: staging box toggle
+    const bool lane_elect = elect_one();            // the lane that issues this warp's TMA stores / barrier arrivals
     const uint64_t store_policy = l2_policy_evict_first();
     for (int u = cid; u < num_units; u += ncl) {
       const Unit t = decode_unit(p, u);
@@ -269,7 +277,7 @@ umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
         auto release = [&]() {                      // one arrival per warp hands the accumulator stage back to the MMA thread
           tc_fence_before();
           __syncwarp();
-          if (lane == 0) {
+          if (lane_elect) {
             if (PAIR) mbar_arrive_leader(&tempty_bar[as]); else mbar_arrive(&tempty_bar[as]);
           }
           released = true;
@@ -284,11 +292,11 @@ umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
             // (store_wide: one [32 x 64] block, 4 KiB, 128B-swizzled, filled by two consecutive chunks and stored once.)
             if (p.store_wide) {
               if ((cc & 1) == 0) {
-                if (lane == 0) bulk_wait_read_all();   // this warp's previous store has drained the block
+                if (lane_elect) bulk_wait_read_all();  // this warp's previous store has drained the block
                 __syncwarp();
               }
             } else {
-              if (lane == 0) bulk_wait_read_1();     // the store issued two blocks ago has drained its buffer
+              if (lane_elect) bulk_wait_read_1();    // the store issued two blocks ago has drained its buffer
               __syncwarp();
             }
           }
@@ -312,7 +320,7 @@ umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
               if (h == 1 || cc + 1 == nch) {         // block complete (a lone first half: the rest lies beyond the matrix edge)
                 fence_proxy_async_smem();
                 __syncwarp();
-                if (lane == 0) {
+                if (lane_elect) {
                   tma_store_2d_hint(&tmD, box, colbase + (cc >> 1) * 64, m0 + q * 32, store_policy);
                   bulk_commit();
                 }
@@ -326,7 +334,7 @@ umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
               st_shared_v4(rowp + ((k ^ ((lane >> 1) & 3)) << 4), w[4 * k], w[4 * k + 1], w[4 * k + 2], w[4 * k + 3]);
             fence_proxy_async_smem();                // generic-proxy writes -> visible to the TMA engine
             __syncwarp();
-            if (lane == 0) {
+            if (lane_elect) {
               // written once, read later by other kernels: do not let it displace the W tiles being re-read from L2
               tma_store_2d_hint(&tmD, box, col0, m0 + q * 32, store_policy);
               bulk_commit();
@@ -465,9 +473,9 @@ umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
         if (z_found) p.zt[row] = zval;
       }
     }
+    if (mode_stores(MODE) && lane_elect) bulk_wait_all();   // this warp's last stores have landed (same lane that issued them)
   }
 
-  if (mode_stores(MODE) && warp >= 4 && lane == 0) bulk_wait_all();   // this warp's last stores have landed   // the last tile's store has landed
   tc_fence_before();
   if (PAIR) cluster_sync_all(); else __syncthreads();    // neither CTA of a pair may leave while the other still needs it
   if (warp == 2) {

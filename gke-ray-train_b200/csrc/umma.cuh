@@ -54,6 +54,16 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
   }
 }
 
+// One lane of the (converged) warp is elected; the others get false. Code that issues the single-thread tcgen05 / TMA
+// instructions under this predicate — instead of under `lane == 0` — stays warp-uniform for the compiler: loop counters and
+// descriptors live in uniform registers and the instruction is issued once, without the per-active-lane ELECT / BRA.U.ANY
+// loop that a divergent branch costs.
+__device__ __forceinline__ bool elect_one() {
+  uint32_t pred;
+  asm volatile("{\n\t.reg .pred p;\n\telect.sync _|p, 0xffffffff;\n\tselp.u32 %0, 1, 0, p;\n\t}" : "=r"(pred));
+  return pred != 0;
+}
+
 // ---------------------------------------------------------------- TMA
 __device__ __forceinline__ void tma_prefetch_desc(const CUtensorMap* m) {
   asm volatile("prefetch.tensormap [%0];" :: "l"(reinterpret_cast<uint64_t>(m)) : "memory");
