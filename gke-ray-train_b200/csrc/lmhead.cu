@@ -156,6 +156,7 @@ umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
     {
       // the whole warp runs the loops; one elected lane issues the expect_tx and the TMA loads (see umma::elect_one)
       const bool issuer = elect_one();
+      const uint32_t full0 = pin_smem(&full_bar[0]), empty0 = pin_smem(&empty_bar[0]), ring0 = pin_smem(smem);
       int stage = 0; uint32_t phase = 0;
       for (int u = cid; u < num_units; u += ncl) {
         const Unit t = decode_unit(p, u);
@@ -163,13 +164,14 @@ umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
         for (int nb = t.nb0; nb < t.nb1; ++nb) {
           const int n0 = nb * BN + crank * BN_CTA;    // first column of B this CTA loads
           for (int kb = t.kb0; kb < t.kb1; ++kb) {
-            mbar_wait(&empty_bar[stage], phase ^ 1);
+            mbar_wait(empty0 + (uint32_t)stage * 8u, phase ^ 1);
             if (!issuer) { if (++stage == STAGES) { stage = 0; phase ^= 1; } continue; }
-            if (crank == 0) mbar_arrive_expect_tx(&full_bar[stage], NC * STAGE_BYTES);
-            uint8_t* sa = smem + stage * STAGE_BYTES;
-            uint8_t* sb = sa + A_STAGE_BYTES;
-            auto load = [&](void* dst, const CUtensorMap* m, int c0, int c1) {
-              if (PAIR) tma_load_2d_pair(dst, m, &full_bar[stage], c0, c1); else tma_load_2d(dst, m, &full_bar[stage], c0, c1);
+            const uint32_t fullb = full0 + (uint32_t)stage * 8u;
+            if (crank == 0) mbar_arrive_expect_tx(fullb, NC * STAGE_BYTES);
+            const uint32_t sa = ring0 + (uint32_t)(stage * STAGE_BYTES);
+            const uint32_t sb = sa + A_STAGE_BYTES;
+            auto load = [&](uint32_t dst, const CUtensorMap* m, int c0, int c1) {
+              if (PAIR) tma_load_2d_pair(dst, m, fullb, c0, c1); else tma_load_2d(dst, m, fullb, c0, c1);
             };
             if (!A_MN) load(sa, &tmA, kb * BK, m0);
             else {
@@ -194,17 +196,19 @@ umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
       constexpr uint32_t idesc = make_idesc_bf16(BM * NC, BN, A_MN, B_MN);
       int stage = 0; uint32_t phase = 0;
       int as = 0; uint32_t aphase = 0;
+      const uint32_t full0 = pin_smem(&full_bar[0]), empty0 = pin_smem(&empty_bar[0]);
+      const uint32_t tfull0 = pin_smem(&tfull_bar[0]), tempty0 = pin_smem(&tempty_bar[0]);
       const uint32_t a_addr0 = smem_u32(smem), b_addr0 = a_addr0 + A_STAGE_BYTES;
       const uint64_t adesc0 = A_MN ? make_sdesc_sw128(a_addr0, BOX_MN_BYTES, 1024) : make_sdesc_sw128(a_addr0, 16, 1024);
       const uint64_t bdesc0 = B_MN ? make_sdesc_sw128(b_addr0, BOX_MN_BYTES, 1024) : make_sdesc_sw128(b_addr0, 16, 1024);
       for (int u = cid; u < num_units; u += ncl) {
         const Unit t = decode_unit(p, u);
         for (int nb = t.nb0; nb < t.nb1; ++nb) {
-          mbar_wait(&tempty_bar[as], aphase ^ 1);
+          mbar_wait(tempty0 + (uint32_t)as * 8u, aphase ^ 1);
           tc_fence_after();
           const uint32_t tmem_d = tmem_base + (uint32_t)(as * BN);
           for (int kb = t.kb0; kb < t.kb1; ++kb) {
-            mbar_wait(&full_bar[stage], phase);
+            mbar_wait(full0 + (uint32_t)stage * 8u, phase);
             tc_fence_after();
             // descriptors differ from the stage-0 / k-0 ones only in the 14-bit start-address field (16-byte units)
             const uint64_t adesc_s = adesc0 + (uint64_t)((uint32_t)(stage * STAGE_BYTES) >> 4);
@@ -218,12 +222,12 @@ umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
                 else mma_bf16_ss(tmem_d, adesc, bdesc, idesc, (uint32_t)(kb > t.kb0 || k > 0));
               }
               // frees the smem slot (in both CTAs of a pair) once these MMAs retire
-              if (PAIR) mma_commit_pair(&empty_bar[stage]); else mma_commit(&empty_bar[stage]);
+              if (PAIR) mma_commit_pair(empty0 + (uint32_t)stage * 8u); else mma_commit(empty0 + (uint32_t)stage * 8u);
             }
             if (++stage == STAGES) { stage = 0; phase ^= 1; }
           }
           // accumulator tile complete (each CTA of a pair reads its own 128 rows from its own TMEM)
-          if (issuer) { if (PAIR) mma_commit_pair(&tfull_bar[as]); else mma_commit(&tfull_bar[as]); }
+          if (issuer) { if (PAIR) mma_commit_pair(tfull0 + (uint32_t)as * 8u); else mma_commit(tfull0 + (uint32_t)as * 8u); }
           as ^= 1; if (as == 0) aphase ^= 1;
         }
       }
