@@ -81,6 +81,7 @@ struct Params {
   float2* part; long long part_stride; float* zt;
   const float* lse; const float* gscale; __nv_bfloat16* dlogits; long long ldd;
   int store_wide;                    // storing modes: 1 = one [32 x 64] TMA store per two chunks, 0 = one [32 x 32] per chunk
+  int debug_store;                   // measurement aid (B2_DEBUG_STORE): 1 = stage the tile but issue no TMA store, 2 = drop it
 };
 
 __device__ __forceinline__ long long label_at(const Params& p, long long i) {
@@ -311,6 +312,7 @@ umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
           // storing modes: this thread's 32 values (one row of the warp's [32 x 32] block) -> 64B-swizzled staging box ->
           // one TMA store per warp
           auto store_block = [&](const float (&v)[32]) {
+            if (p.debug_store == 2) return;          // measurement aid: results are wrong, only the timing means something
             uint32_t w[16];
 #pragma unroll
             for (int j = 0; j < 32; j += 2) w[j >> 1] = pack_bf16(v[j], v[j + 1]);
@@ -324,7 +326,7 @@ umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
               if (h == 1 || cc + 1 == nch) {         // block complete (a lone first half: the rest lies beyond the matrix edge)
                 fence_proxy_async_smem();
                 __syncwarp();
-                if (lane_elect) {
+                if (lane_elect && p.debug_store == 0) {
                   tma_store_2d_hint(&tmD, box, colbase + (cc >> 1) * 64, m0 + q * 32, store_policy);
                   bulk_commit();
                 }
@@ -639,6 +641,10 @@ int num_sms() {
 }
 
 // Shape of the TMA stores of the storing epilogues: [32 x 64] (one per two chunks; default) or [32 x 32] (B2_STORE_BOX=32)
+int debug_store() {
+  static const int v = [] { const char* e = getenv("B2_DEBUG_STORE"); return e == nullptr ? 0 : atoi(e); }();
+  return v;
+}
 bool store_wide() {
   static const bool wide = [] { const char* e = getenv("B2_STORE_BOX"); return e == nullptr ? true : atoi(e) == 64; }();
   return wide;
@@ -827,7 +833,7 @@ static int lmhead_ce_fwd_impl(const void* H, long long ldh, const void* W, long 
     } else {
       CUtensorMap td;
       if ((rc = make_store_tmap(&td, logits_out, V, N, ldl, "b2_lmhead_ce_fwd_keep logits")) != B2_OK) return rc;
-      p.store_wide = store_wide();
+      p.store_wide = store_wide(); p.debug_store = debug_store();
       if ((rc = launch<MODE_CE_FWD_KEEP, 0, 0>(ta, tb, td, p, stream)) != B2_OK) return rc;
     }
     ce_combine_kernel<<<(unsigned)((N + 255) / 256), 256, 0, stream>>>(p.part, p.part_stride, 2 * p.n_splits, N, lse);
@@ -898,6 +904,6 @@ extern "C" int b2_lmhead_ce_bwd_dlogits(const void* H, long long ldh, const void
   p.lse = lse; p.gscale = gscale_dev; p.dlogits = static_cast<__nv_bfloat16*>(dlogits); p.ldd = ldd;
   CUtensorMap td;
   if ((rc = make_store_tmap(&td, dlogits, V, rows, ldd, "b2_lmhead_ce_bwd_dlogits dlogits")) != B2_OK) return rc;
-  p.store_wide = store_wide();
+  p.store_wide = store_wide(); p.debug_store = debug_store();
   return launch<MODE_CE_BWD, 0, 0>(ta, tb, td, p, stream);
 }
