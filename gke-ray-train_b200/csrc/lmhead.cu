@@ -81,6 +81,7 @@ struct Params {
   float2* part; long long part_stride; float* zt;
   const float* lse; const float* gscale; __nv_bfloat16* dlogits; long long ldd;
   int store_wide;                    // storing modes: 1 = one [32 x 64] TMA store per two chunks, 0 = one [32 x 32] per chunk
+  int debug_store;                   // measurement aid (B2_DEBUG_STORE): 1 = stage the tile but issue no TMA store, 2 = drop it
 };
 
 __device__ __forceinline__ long long label_at(const Params& p, long long i) {
@@ -153,7 +154,10 @@ umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
 
   if (warp == 0) {
     // ------------------------------------------------------------ TMA producer
-    if (lane == 0) {
+    {
+      // the whole warp runs the loops; one elected lane issues the expect_tx and the TMA loads (see umma::elect_one)
+      const bool issuer = elect_one();
+      const uint32_t full0 = pin_smem(&full_bar[0]), empty0 = pin_smem(&empty_bar[0]), ring0 = pin_smem(smem);
       int stage = 0; uint32_t phase = 0;
       for (int u = cid; u < num_units; u += ncl) {
         const Unit t = decode_unit(p, u);
@@ -161,12 +165,14 @@ umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
         for (int nb = t.nb0; nb < t.nb1; ++nb) {
           const int n0 = nb * BN + crank * BN_CTA;    // first column of B this CTA loads
           for (int kb = t.kb0; kb < t.kb1; ++kb) {
-            mbar_wait(&empty_bar[stage], phase ^ 1);
-            if (crank == 0) mbar_arrive_expect_tx(&full_bar[stage], NC * STAGE_BYTES);
-            uint8_t* sa = smem + stage * STAGE_BYTES;
-            uint8_t* sb = sa + A_STAGE_BYTES;
-            auto load = [&](void* dst, const CUtensorMap* m, int c0, int c1) {
-              if (PAIR) tma_load_2d_pair(dst, m, &full_bar[stage], c0, c1); else tma_load_2d(dst, m, &full_bar[stage], c0, c1);
+            mbar_wait(empty0 + (uint32_t)stage * 8u, phase ^ 1);
+            if (!issuer) { if (++stage == STAGES) { stage = 0; phase ^= 1; } continue; }
+            const uint32_t fullb = full0 + (uint32_t)stage * 8u;
+            if (crank == 0) mbar_arrive_expect_tx(fullb, NC * STAGE_BYTES);
+            const uint32_t sa = ring0 + (uint32_t)(stage * STAGE_BYTES);
+            const uint32_t sb = sa + A_STAGE_BYTES;
+            auto load = [&](uint32_t dst, const CUtensorMap* m, int c0, int c1) {
+              if (PAIR) tma_load_2d_pair(dst, m, fullb, c0, c1); else tma_load_2d(dst, m, fullb, c0, c1);
             };
             if (!A_MN) load(sa, &tmA, kb * BK, m0);
             else {
@@ -185,38 +191,44 @@ umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
     }
   } else if (warp == 1) {
     // ------------------------------------------------------------ MMA issuer (one thread)
-    if (lane == 0 && crank == 0) {
+    if (crank == 0) {
+      // the whole warp runs the loops (warp-uniform control flow); one elected lane issues the MMAs and commits
+      const bool issuer = elect_one();
       constexpr uint32_t idesc = make_idesc_bf16(BM * NC, BN, A_MN, B_MN);
       int stage = 0; uint32_t phase = 0;
       int as = 0; uint32_t aphase = 0;
+      const uint32_t full0 = pin_smem(&full_bar[0]), empty0 = pin_smem(&empty_bar[0]);
+      const uint32_t tfull0 = pin_smem(&tfull_bar[0]), tempty0 = pin_smem(&tempty_bar[0]);
       const uint32_t a_addr0 = smem_u32(smem), b_addr0 = a_addr0 + A_STAGE_BYTES;
       const uint64_t adesc0 = A_MN ? make_sdesc_sw128(a_addr0, BOX_MN_BYTES, 1024) : make_sdesc_sw128(a_addr0, 16, 1024);
       const uint64_t bdesc0 = B_MN ? make_sdesc_sw128(b_addr0, BOX_MN_BYTES, 1024) : make_sdesc_sw128(b_addr0, 16, 1024);
       for (int u = cid; u < num_units; u += ncl) {
         const Unit t = decode_unit(p, u);
         for (int nb = t.nb0; nb < t.nb1; ++nb) {
-          mbar_wait(&tempty_bar[as], aphase ^ 1);
+          mbar_wait(tempty0 + (uint32_t)as * 8u, aphase ^ 1);
           tc_fence_after();
           const uint32_t tmem_d = tmem_base + (uint32_t)(as * BN);
           for (int kb = t.kb0; kb < t.kb1; ++kb) {
-            mbar_wait(&full_bar[stage], phase);
+            mbar_wait(full0 + (uint32_t)stage * 8u, phase);
             tc_fence_after();
             // descriptors differ from the stage-0 / k-0 ones only in the 14-bit start-address field (16-byte units)
             const uint64_t adesc_s = adesc0 + (uint64_t)((uint32_t)(stage * STAGE_BYTES) >> 4);
             const uint64_t bdesc_s = bdesc0 + (uint64_t)((uint32_t)(stage * STAGE_BYTES) >> 4);
+            if (issuer) {
 #pragma unroll
-            for (int k = 0; k < BK / UK; ++k) {
-              const uint64_t adesc = adesc_s + (uint64_t)((A_MN ? k * (UK * 128) : k * (UK * 2)) >> 4);
-              const uint64_t bdesc = bdesc_s + (uint64_t)((B_MN ? k * (UK * 128) : k * (UK * 2)) >> 4);
-              if (PAIR) mma_bf16_ss_pair(tmem_d, adesc, bdesc, idesc, (uint32_t)(kb > t.kb0 || k > 0));
-              else mma_bf16_ss(tmem_d, adesc, bdesc, idesc, (uint32_t)(kb > t.kb0 || k > 0));
+              for (int k = 0; k < BK / UK; ++k) {
+                const uint64_t adesc = adesc_s + (uint64_t)((A_MN ? k * (UK * 128) : k * (UK * 2)) >> 4);
+                const uint64_t bdesc = bdesc_s + (uint64_t)((B_MN ? k * (UK * 128) : k * (UK * 2)) >> 4);
+                if (PAIR) mma_bf16_ss_pair(tmem_d, adesc, bdesc, idesc, (uint32_t)(kb > t.kb0 || k > 0));
+                else mma_bf16_ss(tmem_d, adesc, bdesc, idesc, (uint32_t)(kb > t.kb0 || k > 0));
+              }
+              // frees the smem slot (in both CTAs of a pair) once these MMAs retire
+              if (PAIR) mma_commit_pair(empty0 + (uint32_t)stage * 8u); else mma_commit(empty0 + (uint32_t)stage * 8u);
             }
-            // frees the smem slot (in both CTAs of a pair) once these MMAs retire
-            if (PAIR) mma_commit_pair(&empty_bar[stage]); else mma_commit(&empty_bar[stage]);
             if (++stage == STAGES) { stage = 0; phase ^= 1; }
           }
           // accumulator tile complete (each CTA of a pair reads its own 128 rows from its own TMEM)
-          if (PAIR) mma_commit_pair(&tfull_bar[as]); else mma_commit(&tfull_bar[as]);
+          if (issuer) { if (PAIR) mma_commit_pair(tfull0 + (uint32_t)as * 8u); else mma_commit(tfull0 + (uint32_t)as * 8u); }
           as ^= 1; if (as == 0) aphase ^= 1;
         }
       }
@@ -230,6 +242,7 @@ umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
     const int trow = q * 32 + lane;                 // row inside the tile
     int as = 0; uint32_t aphase = 0;
     uint32_t store_seq = 0;                         // storing modes: staging box toggle
+    const bool lane_elect = elect_one();            // the lane that issues this warp's TMA stores / barrier arrivals
     const uint64_t store_policy = l2_policy_evict_first();
     for (int u = cid; u < num_units; u += ncl) {
       const Unit t = decode_unit(p, u);
@@ -269,7 +282,7 @@ umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
         auto release = [&]() {                      // one arrival per warp hands the accumulator stage back to the MMA thread
           tc_fence_before();
           __syncwarp();
-          if (lane == 0) {
+          if (lane_elect) {
             if (PAIR) mbar_arrive_leader(&tempty_bar[as]); else mbar_arrive(&tempty_bar[as]);
           }
           released = true;
@@ -284,11 +297,11 @@ umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
             // (store_wide: one [32 x 64] block, 4 KiB, 128B-swizzled, filled by two consecutive chunks and stored once.)
             if (p.store_wide) {
               if ((cc & 1) == 0) {
-                if (lane == 0) bulk_wait_read_all();   // this warp's previous store has drained the block
+                if (lane_elect) bulk_wait_read_all();  // this warp's previous store has drained the block
                 __syncwarp();
               }
             } else {
-              if (lane == 0) bulk_wait_read_1();     // the store issued two blocks ago has drained its buffer
+              if (lane_elect) bulk_wait_read_1();    // the store issued two blocks ago has drained its buffer
               __syncwarp();
             }
           }
@@ -299,6 +312,7 @@ umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
           // storing modes: this thread's 32 values (one row of the warp's [32 x 32] block) -> 64B-swizzled staging box ->
           // one TMA store per warp
           auto store_block = [&](const float (&v)[32]) {
+            if (p.debug_store == 2) return;          // measurement aid: results are wrong, only the timing means something
             uint32_t w[16];
 #pragma unroll
             for (int j = 0; j < 32; j += 2) w[j >> 1] = pack_bf16(v[j], v[j + 1]);
@@ -312,7 +326,7 @@ umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
               if (h == 1 || cc + 1 == nch) {         // block complete (a lone first half: the rest lies beyond the matrix edge)
                 fence_proxy_async_smem();
                 __syncwarp();
-                if (lane == 0) {
+                if (lane_elect && p.debug_store == 0) {
                   tma_store_2d_hint(&tmD, box, colbase + (cc >> 1) * 64, m0 + q * 32, store_policy);
                   bulk_commit();
                 }
@@ -326,7 +340,7 @@ umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
               st_shared_v4(rowp + ((k ^ ((lane >> 1) & 3)) << 4), w[4 * k], w[4 * k + 1], w[4 * k + 2], w[4 * k + 3]);
             fence_proxy_async_smem();                // generic-proxy writes -> visible to the TMA engine
             __syncwarp();
-            if (lane == 0) {
+            if (lane_elect) {
               // written once, read later by other kernels: do not let it displace the W tiles being re-read from L2
               tma_store_2d_hint(&tmD, box, col0, m0 + q * 32, store_policy);
               bulk_commit();
@@ -465,9 +479,9 @@ umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
         if (z_found) p.zt[row] = zval;
       }
     }
+    if (mode_stores(MODE) && lane_elect) bulk_wait_all();   // this warp's last stores have landed (same lane that issued them)
   }
 
-  if (mode_stores(MODE) && warp >= 4 && lane == 0) bulk_wait_all();   // this warp's last stores have landed   // the last tile's store has landed
   tc_fence_before();
   if (PAIR) cluster_sync_all(); else __syncthreads();    // neither CTA of a pair may leave while the other still needs it
   if (warp == 2) {
@@ -627,6 +641,10 @@ int num_sms() {
 }
 
 // Shape of the TMA stores of the storing epilogues: [32 x 64] (one per two chunks; default) or [32 x 32] (B2_STORE_BOX=32)
+int debug_store() {
+  static const int v = [] { const char* e = getenv("B2_DEBUG_STORE"); return e == nullptr ? 0 : atoi(e); }();
+  return v;
+}
 bool store_wide() {
   static const bool wide = [] { const char* e = getenv("B2_STORE_BOX"); return e == nullptr ? true : atoi(e) == 64; }();
   return wide;
@@ -815,7 +833,7 @@ static int lmhead_ce_fwd_impl(const void* H, long long ldh, const void* W, long 
     } else {
       CUtensorMap td;
       if ((rc = make_store_tmap(&td, logits_out, V, N, ldl, "b2_lmhead_ce_fwd_keep logits")) != B2_OK) return rc;
-      p.store_wide = store_wide();
+      p.store_wide = store_wide(); p.debug_store = debug_store();
       if ((rc = launch<MODE_CE_FWD_KEEP, 0, 0>(ta, tb, td, p, stream)) != B2_OK) return rc;
     }
     ce_combine_kernel<<<(unsigned)((N + 255) / 256), 256, 0, stream>>>(p.part, p.part_stride, 2 * p.n_splits, N, lse);
@@ -886,6 +904,6 @@ extern "C" int b2_lmhead_ce_bwd_dlogits(const void* H, long long ldh, const void
   p.lse = lse; p.gscale = gscale_dev; p.dlogits = static_cast<__nv_bfloat16*>(dlogits); p.ldd = ldd;
   CUtensorMap td;
   if ((rc = make_store_tmap(&td, dlogits, V, rows, ldd, "b2_lmhead_ce_bwd_dlogits dlogits")) != B2_OK) return rc;
-  p.store_wide = store_wide();
+  p.store_wide = store_wide(); p.debug_store = debug_store();
   return launch<MODE_CE_BWD, 0, 0>(ta, tb, td, p, stream);
 }

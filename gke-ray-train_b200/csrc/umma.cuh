@@ -9,6 +9,14 @@
 namespace umma {
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+// The same address, pinned in a register. Left alone the compiler re-derives a shared-memory address from its generic
+// pointer at every use (on sm_100: S2UR SR_CgaCtaId + ULEA, a long-latency pair) — too expensive inside the loops of the
+// single thread that issues the MMAs or the TMA loads. The empty asm makes the value opaque, so it is computed once.
+__device__ __forceinline__ uint32_t pin_smem(const void* p) {
+  uint32_t a = smem_u32(p);
+  asm volatile("" : "+r"(a));
+  return a;
+}
 
 // ---------------------------------------------------------------- mbarrier
 __device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
@@ -19,18 +27,21 @@ __device__ __forceinline__ void fence_proxy_async_smem() { asm volatile("fence.p
 __device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
   asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" :: "r"(smem_u32(bar)) : "memory");
 }
-__device__ __forceinline__ void mbar_arrive_expect_tx(uint64_t* bar, uint32_t bytes) {
-  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" :: "r"(smem_u32(bar)), "r"(bytes) : "memory");
+// (every barrier helper exists in two forms: by pointer, and by pinned 32-bit shared address — see pin_smem)
+__device__ __forceinline__ void mbar_arrive_expect_tx(uint32_t bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" :: "r"(bar), "r"(bytes) : "memory");
 }
-__device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
+__device__ __forceinline__ void mbar_arrive_expect_tx(uint64_t* bar, uint32_t bytes) { mbar_arrive_expect_tx(smem_u32(bar), bytes); }
+__device__ __forceinline__ bool mbar_try_wait(uint32_t bar, uint32_t parity) {
   uint32_t ok;
   asm volatile(
       "{\n\t.reg .pred p;\n\t"
       "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
       "selp.b32 %0, 1, 0, p;\n\t}"
-      : "=r"(ok) : "r"(smem_u32(bar)), "r"(parity) : "memory");
+      : "=r"(ok) : "r"(bar), "r"(parity) : "memory");
   return ok != 0;
 }
+__device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) { return mbar_try_wait(smem_u32(bar), parity); }
 __device__ __forceinline__ uint64_t globaltimer_ns() {
   uint64_t t;
   asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
@@ -38,7 +49,7 @@ __device__ __forceinline__ uint64_t globaltimer_ns() {
 }
 // Waits for the phase with the given parity to complete. A wait that lasts longer than ~4 s is a
 // protocol bug (or a peer that died): trap so the launch fails loudly instead of hanging the GPU.
-__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
   if (mbar_try_wait(bar, parity)) return;
   uint64_t t0 = 0;
   uint32_t spins = 0;
@@ -53,17 +64,31 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
     }
   }
 }
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) { mbar_wait(smem_u32(bar), parity); }
+
+// One lane of the (converged) warp is elected; the others get false. Code that issues the single-thread tcgen05 / TMA
+// instructions under this predicate — instead of under `lane == 0` — stays warp-uniform for the compiler: loop counters and
+// descriptors live in uniform registers and the instruction is issued once, without the per-active-lane ELECT / BRA.U.ANY
+// loop that a divergent branch costs.
+__device__ __forceinline__ bool elect_one() {
+  uint32_t pred;
+  asm volatile("{\n\t.reg .pred p;\n\telect.sync _|p, 0xffffffff;\n\tselp.u32 %0, 1, 0, p;\n\t}" : "=r"(pred));
+  return pred != 0;
+}
 
 // ---------------------------------------------------------------- TMA
 __device__ __forceinline__ void tma_prefetch_desc(const CUtensorMap* m) {
   asm volatile("prefetch.tensormap [%0];" :: "l"(reinterpret_cast<uint64_t>(m)) : "memory");
 }
 // 2-D tiled load: coordinates are (c0 = innermost/contiguous dim, c1 = outer dim), in elements.
-__device__ __forceinline__ void tma_load_2d(void* smem_dst, const CUtensorMap* m, uint64_t* bar, int c0, int c1) {
+__device__ __forceinline__ void tma_load_2d(uint32_t smem_dst, const CUtensorMap* m, uint32_t bar, int c0, int c1) {
   asm volatile(
       "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
-      :: "r"(smem_u32(smem_dst)), "l"(reinterpret_cast<uint64_t>(m)), "r"(smem_u32(bar)), "r"(c0), "r"(c1)
+      :: "r"(smem_dst), "l"(reinterpret_cast<uint64_t>(m)), "r"(bar), "r"(c0), "r"(c1)
       : "memory");
+}
+__device__ __forceinline__ void tma_load_2d(void* smem_dst, const CUtensorMap* m, uint64_t* bar, int c0, int c1) {
+  tma_load_2d(smem_u32(smem_dst), m, smem_u32(bar), c0, c1);
 }
 
 // L2 eviction policies for the hints below: data that is streamed once should not push reused operand tiles out of L2
@@ -131,10 +156,10 @@ __device__ __forceinline__ void mma_bf16_ss(uint32_t tmem_d, uint64_t desc_a, ui
 }
 // Arrive on `bar` once every tcgen05.mma issued so far by this thread has completed.
 // (Implies tcgen05.fence::before_thread_sync.)
-__device__ __forceinline__ void mma_commit(uint64_t* bar) {
-  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];"
-               :: "r"(smem_u32(bar)) : "memory");
+__device__ __forceinline__ void mma_commit(uint32_t bar) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" :: "r"(bar) : "memory");
 }
+__device__ __forceinline__ void mma_commit(uint64_t* bar) { mma_commit(smem_u32(bar)); }
 
 // Warp w (w%4 = q) may touch TMEM lanes [32q, 32q+32). Lane i of the warp gets row 32q+i,
 // 32 consecutive fp32 columns starting at the address' column.
@@ -175,11 +200,14 @@ __device__ __forceinline__ void cluster_sync_all() {
   asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
 }
 // TMA load whose completion bytes are credited to the LEADER CTA's mbarrier (same offset as `bar` here)
-__device__ __forceinline__ void tma_load_2d_pair(void* smem_dst, const CUtensorMap* m, uint64_t* bar, int c0, int c1) {
+__device__ __forceinline__ void tma_load_2d_pair(uint32_t smem_dst, const CUtensorMap* m, uint32_t bar, int c0, int c1) {
   asm volatile(
       "cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
-      :: "r"(smem_u32(smem_dst)), "l"(reinterpret_cast<uint64_t>(m)), "r"(smem_u32(bar) & kPeerBitMask), "r"(c0), "r"(c1)
+      :: "r"(smem_dst), "l"(reinterpret_cast<uint64_t>(m)), "r"(bar & kPeerBitMask), "r"(c0), "r"(c1)
       : "memory");
+}
+__device__ __forceinline__ void tma_load_2d_pair(void* smem_dst, const CUtensorMap* m, uint64_t* bar, int c0, int c1) {
+  tma_load_2d_pair(smem_u32(smem_dst), m, smem_u32(bar), c0, c1);
 }
 // arrive on the leader CTA's copy of `bar` (works from either CTA of the pair)
 __device__ __forceinline__ void mbar_arrive_leader(uint64_t* bar) {
@@ -204,11 +232,12 @@ __device__ __forceinline__ void mma_bf16_ss_pair(uint32_t tmem_d, uint64_t desc_
       :: "r"(tmem_d), "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate) : "memory");
 }
 // arrive on `bar` in BOTH CTAs of the pair once the pair MMAs issued so far have completed
-__device__ __forceinline__ void mma_commit_pair(uint64_t* bar) {
+__device__ __forceinline__ void mma_commit_pair(uint32_t bar) {
   const uint16_t mask = 3;
   asm volatile("tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;"
-               :: "r"(smem_u32(bar)), "h"(mask) : "memory");
+               :: "r"(bar), "h"(mask) : "memory");
 }
+__device__ __forceinline__ void mma_commit_pair(uint64_t* bar) { mma_commit_pair(smem_u32(bar)); }
 
 // ---------------------------------------------------------------- descriptors
 // Instruction descriptor, kind::f16: bf16 x bf16 -> fp32, dense, no negate.
