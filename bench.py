@@ -152,7 +152,7 @@ def f1_roofline(torch, b200, model, device, peaks, iters=5):
     y = labels.reshape(-1)
     Hd, Wd = H.detach(), Wl.detach()
     r = ops.lmhead_ce_fwd(Hd, Wd, y, shift_T=SEQ)
-    ldd = (V + 7) // 8 * 8
+    ldd = (V + 63) // 64 * 64          # row pitch: a multiple of 128 bytes
     dl = torch.empty(N, ldd, dtype=torch.bfloat16, device=device)
     dH = torch.empty(N, D, dtype=torch.bfloat16, device=device)
     dW = torch.empty(V, D, dtype=torch.bfloat16, device=device)

@@ -71,10 +71,11 @@ _SIGS = {
     "b2_symm_close": (c_int, [c_void_p]),
     "b2_symm_free": (c_int, [c_void_p]),
     "b2_peer_allreduce": (c_int, [c_void_p, c_void_p, c_int, c_int, c_size_t, c_size_t, c_int, c_float, ctypes.c_uint,
-                                  c_int, c_int, c_int, c_void_p]),
+                                  c_int, c_int, c_int, c_void_p, c_void_p]),
     "b2_peer_allreduce_mc": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_size_t, c_size_t, c_int, c_float,
-                                     ctypes.c_uint, c_int, c_int, c_int, c_void_p]),
-    "b2_peer_allgather": (c_int, [c_void_p, c_void_p, c_int, c_int, c_size_t, c_size_t, c_int, ctypes.c_uint, c_void_p]),
+                                     ctypes.c_uint, c_int, c_int, c_int, c_void_p, c_void_p]),
+    "b2_peer_allgather": (c_int, [c_void_p, c_void_p, c_int, c_int, c_size_t, c_size_t, c_int, ctypes.c_uint, c_int,
+                                  c_void_p]),
     "b2_peer_slice": (c_int, [c_size_t, c_int, c_int, c_int, c_void_p, c_void_p]),
     "b2_debug_peer_copy": (c_int, [c_void_p, c_void_p, c_size_t, c_int, c_int, c_int, c_void_p]),
 }

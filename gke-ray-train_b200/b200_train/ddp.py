@@ -10,6 +10,12 @@ The wrapper plays the role of torch.nn.parallel.DistributedDataParallel ($SP/tor
 gradients live in ONE flat buffer per dtype in symmetric memory, and ranges of it ("buckets") are averaged in place over
 NVLink by our peer-memory kernel (b2_peer_allreduce / b2_peer_allreduce_mc) while the rest of backward still runs — no
 bucket copy-in, no NCCL all-reduce, no copy-out.
+
+`parallel_strategy_kwargs={"shard_optimizer": True}` switches to the partitioning SURVEY.md §8(e) describes: each
+bucket is only reduce-SCATTERED during backward (rank r keeps slice r of every bucket), AdamW runs on those slices
+(optimizer state and optimizer HBM traffic divided by the world size), and the updated slices are all-gathered bucket by
+bucket, front of the model first, on the side stream — under the remaining AdamW launches and, with
+`"overlap_param_sync": True`, under the next forward pass (each module waits for the bucket that holds its parameters).
 """
 import contextlib
 import os
@@ -24,38 +30,52 @@ from .flat import flatten_params
 from .symm import PeerComm
 
 
+# set by the trainer shim for its workers: ScalingConfig(use_gpu=False) means CPU workers even on a box that has GPUs
+_use_gpu = None
+
+
 def get_device():
-    """`ray.train.torch.get_device()` (ref: ray-jobs/pytorch_llm_ray.py:128): this worker's GPU."""
-    if not torch.cuda.is_available():
+    """`ray.train.torch.get_device()` (ref: ray-jobs/pytorch_llm_ray.py:128): this worker's GPU (the CPU for a worker of
+    a `use_gpu=False` trainer)."""
+    if _use_gpu is False or not torch.cuda.is_available():
         return torch.device("cpu")
     return torch.device("cuda", int(os.environ.get("LOCAL_RANK", "0")) % torch.cuda.device_count())
 
 
-def plan_buckets(offsets, total, esize, cap_bytes):
+def plan_buckets(offsets, total, esize, cap_bytes, front_params=0):
     """Cuts a flat buffer (parameter start offsets `offsets`, `total` elements, `esize` bytes each) into contiguous
     ranges from its END, each closed as soon as it holds at least `cap_bytes`; the last one takes whatever is left at the
-    front. Returns [(start, numel, [parameter indices])] in launch order (last parameters first)."""
+    front. `front_params` > 0 makes the first that many parameters a bucket of their own: the embeddings sit at the front
+    of the buffer and their gradient is the LAST one backward produces (for a tied LM head: only after the embedding
+    lookup's backward), so everything else must not wait for them. Returns [(start, numel, [parameter indices])] in
+    launch order (last parameters first)."""
     out, end, members = [], total, []
-    for i in range(len(offsets) - 1, -1, -1):
+    floor = front_params if 0 < front_params < len(offsets) else 0
+    for i in range(len(offsets) - 1, floor - 1, -1):
         members.append(i)
         start = offsets[i] if i > 0 else 0
-        if (end - start) * esize >= cap_bytes or i == 0:
+        if (end - start) * esize >= cap_bytes or i == floor:
             out.append((start, end - start, members))
             end, members = start, []
+    if floor:
+        out.append((0, end, list(range(floor - 1, -1, -1))))
     return out
 
 
 class _Bucket:
     """A contiguous element range of one flat gradient buffer, reduced by one kernel launch."""
-    __slots__ = ("buf", "offset", "numel", "nparams", "pending")
+    __slots__ = ("buf", "offset", "numel", "nparams", "pending", "shard", "ag_event", "key")
 
-    def __init__(self, buf, offset, numel, nparams):
+    def __init__(self, buf, offset, numel, nparams, key):
         self.buf, self.offset, self.numel, self.nparams, self.pending = buf, offset, numel, nparams, nparams
+        self.shard = None          # (begin, end) of this rank's slice, in buffer elements (sharded optimizer)
+        self.ag_event = None
+        self.key = key
 
 
 class DistributedDataParallel(nn.Module):
     def __init__(self, module, device_ids=None, output_device=None, process_group=None, broadcast_buffers=True,
-                 bucket_cap_mb=None, overlap=True, shard_optimizer=False, **unused):
+                 bucket_cap_mb=None, overlap=True, shard_optimizer=False, overlap_param_sync=False, **unused):
         super().__init__()
         if not dist.is_initialized():
             raise B2Error("DistributedDataParallel needs an initialised torch.distributed process group")
@@ -72,17 +92,18 @@ class DistributedDataParallel(nn.Module):
         self.world_size = dist.get_world_size(process_group)
         self.comm = PeerComm(device, process_group)
         self.flat_buffers = flatten_params(params, alloc=self.comm.alloc)   # (not `buffers`: that is nn.Module's method)
+        for buf in self.flat_buffers:
+            if getattr(buf.data, "_b2_symm", None) is None or getattr(buf.grad, "_b2_symm", None) is None:
+                raise B2Error("prepare_model found parameters that a b200_train.AdamW has already moved into ordinary "
+                              "device memory; the peer-memory all-reduce needs them in symmetric memory. Create the "
+                              "optimizer AFTER prepare_model(model), as the reference does (pytorch_llm_ray.py:230,236)")
         self.shard_optimizer = bool(shard_optimizer)
         # DDP's _sync_module_states: every rank starts from rank 0's weights and buffers (bootstrap over NCCL)
         for buf in self.flat_buffers:
             dist.broadcast(buf.data, src=0, group=process_group)
             buf.comm = self.comm
             buf.reduced_sumsq = None
-            if self.shard_optimizer:
-                # ZeRO-1 style: rank r reduces, clips and updates only slice r of the flat buffer, then
-                # pushes its slice of the updated parameters to every peer; exp_avg / exp_avg_sq exist for that slice only
-                buf.shard_range = self.comm.slice_bounds(buf.numel, buf.dtype)
-            buf._sumsq_store = torch.empty(self.world_size, dtype=torch.float32, device=device)
+            buf._sumsq_store = torch.zeros(self.world_size, dtype=torch.float32, device=device)
         for b in module.buffers():
             if b.is_cuda:
                 dist.broadcast(b, src=0, group=process_group)
@@ -93,38 +114,76 @@ class DistributedDataParallel(nn.Module):
         # buckets are cut from the END of each buffer and launched in that fixed order on a side stream while the rest
         # of backward still runs.
         # (B2_DDP_OVERLAP / B2_DDP_BUCKET_MB / B2_DDP_MAX_BLOCKS override the arguments for measurements)
-        self.overlap = bool(int(os.environ.get("B2_DDP_OVERLAP", int(bool(overlap))))) and not self.shard_optimizer
+        self.overlap = bool(int(os.environ.get("B2_DDP_OVERLAP", int(bool(overlap)))))
+        self.overlap_param_sync = bool(int(os.environ.get("B2_DDP_PARAM_OVERLAP", int(bool(overlap_param_sync))))) \
+            and self.overlap and self.shard_optimizer
         # measured on GPT-2 124M / 2 GPUs (profiles/README.md): 100 MiB buckets on <= 96 CTAs beat torch's 25 MiB default
         bucket_cap_mb = float(os.environ.get("B2_DDP_BUCKET_MB", 100 if bucket_cap_mb is None else bucket_cap_mb))
         self._overlap_blocks = int(os.environ.get("B2_DDP_MAX_BLOCKS", 96))
         cap_bytes = int(bucket_cap_mb * 1024 * 1024) if self.overlap else (1 << 62)      # no overlap: one launch per buffer
+        emb = {id(p) for m in module.modules() if isinstance(m, nn.Embedding) for p in m.parameters(recurse=False)}
         self._buckets, self._bucket_of = [], {}
         for buf in self.flat_buffers:
-            for start, numel, members in plan_buckets(buf.offsets, buf.numel, buf.data.element_size(), cap_bytes):
+            front = 0
+            while self.overlap and front < len(buf.params) and id(buf.params[front]) in emb:
+                front += 1
+            mine = []
+            for start, numel, members in plan_buckets(buf.offsets, buf.numel, buf.data.element_size(), cap_bytes, front):
                 for j in members:
                     self._bucket_of[id(buf.params[j])] = len(self._buckets)
-                self._buckets.append(_Bucket(buf, start, numel, len(members)))
+                b = _Bucket(buf, start, numel, len(members), len(self._buckets))
+                self._buckets.append(b)
+                mine.append(b)
+            if self.shard_optimizer:
+                # rank r reduces, clips and updates slice r of EVERY bucket, then pushes it to the peers; exp_avg /
+                # exp_avg_sq exist for those slices only. Listed front of the buffer first: that is the order in which
+                # the optimizer updates them and the parameters travel, so the first layers are complete first.
+                mine.sort(key=lambda b: b.offset)
+                so, shards = 0, []
+                for b in mine:
+                    lo, hi = self.comm.slice_bounds(b.numel, buf.dtype)
+                    b.shard = (b.offset + lo, b.offset + hi)
+                    b.ag_event = torch.cuda.Event()
+                    shards.append((b.offset + lo, b.offset + hi, so))
+                    so += hi - lo
+                buf.shards = shards
+                buf._shard_buckets = mine
+                buf.after_shard_update = self._make_shard_sync(buf)
+                buf.param_gate = self._make_param_gate(buf)
         self._next_bucket = 0
         self._comm_stream = torch.cuda.Stream(device=device) if self.overlap else None
+        self._ag_pending = {}
         for p in params:
             p.register_post_accumulate_grad_hook(self._on_grad)
+        if self.overlap_param_sync:
+            self._mod_buckets = {}
+            for m in module.modules():
+                keys = sorted({self._bucket_of[id(p)] for p in m.parameters(recurse=False) if id(p) in self._bucket_of})
+                if keys:
+                    self._mod_buckets[id(m)] = keys
+                    m.register_forward_pre_hook(self._gate_module)
 
     # ------------------------------------------------------------------ backward-side plumbing
-    def _launch_bucket(self, b, tail=False):
-        """Peer-memory all-reduce of one bucket. With overlap it runs on the side stream, ordered after everything the
-        backward stream has enqueued so far, on a capped grid so it shares the SMs with the remaining backward kernels."""
+    def _launch_bucket(self, b, tail, last_of_buf):
+        """Peer-memory all-reduce (or, with a sharded optimizer, reduce-scatter) of one bucket. With overlap it runs on
+        the side stream, ordered after everything the backward stream has enqueued so far, on a capped grid so it shares
+        the SMs with the remaining backward kernels. The launch that completes a buffer also delivers the W per-rank
+        sums of squares (its last act, after the end barrier) into the buffer's own store."""
         first = self._next_bucket == 0 or b.buf is not self._buckets[self._next_bucket - 1].buf
         mode = 1 if first else 2          # sum-of-squares slots: restart on a buffer's first bucket, then keep adding
+        kw = dict(want_sumsq=mode, offset=b.offset, numel=b.numel, scatter_only=self.shard_optimizer,
+                  sumsq_out=b.buf._sumsq_store if last_of_buf else None)
         if self.overlap:
             ev = torch.cuda.Event()
             ev.record(torch.cuda.current_stream())
             self._comm_stream.wait_event(ev)
             with torch.cuda.stream(self._comm_stream):
-                self.comm.allreduce_(b.buf.grad, want_sumsq=mode, offset=b.offset, numel=b.numel,
-                                     max_blocks=0 if tail else self._overlap_blocks)      # nothing left to overlap with: whole GPU
+                # tail: nothing left to overlap with -> whole GPU
+                self.comm.allreduce_(b.buf.grad, max_blocks=0 if tail else self._overlap_blocks, **kw)
         else:
-            self.comm.allreduce_(b.buf.grad, want_sumsq=mode, offset=b.offset, numel=b.numel,
-                                 scatter_only=self.shard_optimizer)
+            self.comm.allreduce_(b.buf.grad, **kw)
+        if last_of_buf:
+            b.buf.reduced_sumsq = b.buf._sumsq_store
 
     def _launch_ready(self, force=False):
         while self._next_bucket < len(self._buckets):
@@ -133,17 +192,12 @@ class DistributedDataParallel(nn.Module):
                 break
             last_of_buf = (self._next_bucket + 1 == len(self._buckets)
                            or self._buckets[self._next_bucket + 1].buf is not b.buf)
-            self._launch_bucket(b, tail=force)
+            self._launch_bucket(b, tail=force, last_of_buf=last_of_buf)
             self._next_bucket += 1
-            if last_of_buf:
-                # the W per-rank partials of this buffer are complete once this launch retires: keep a copy, the slots
-                # are reused by the next buffer / step
-                stream = self._comm_stream if self.overlap else torch.cuda.current_stream()
-                with torch.cuda.stream(stream):
-                    b.buf._sumsq_store.copy_(self.comm._parts)
-                b.buf.reduced_sumsq = b.buf._sumsq_store
 
     def _on_grad(self, p):
+        # (the flat buffer's own hook ran first: p.grad already IS the parameter's slice of the flat gradient buffer,
+        # whatever the caller did to the gradients between forward and backward)
         if not self.require_backward_grad_sync:
             return
         if not self._callback_queued:
@@ -158,8 +212,14 @@ class DistributedDataParallel(nn.Module):
     def _finalize_backward(self):
         """Runs once per backward pass, after the last gradient has been accumulated."""
         self._callback_queued = False
+        self.reduce_gradients()
+
+    def reduce_gradients(self):
+        """Reduces every bucket that has not been launched yet and joins the side stream. Called at the end of each
+        synchronised backward pass; callable by hand after backward passes under `no_sync()` (the buckets, kernels and
+        launch order are the ones the overlapped path uses)."""
         for buf in self.flat_buffers:
-            buf.install_grads()            # a stray .grad (allocated by autograd after a foreign zero_grad) is copied in
+            buf.install_grads()            # parameters that received no gradient contribute zeros
         self._launch_ready(force=True)     # whatever is left (all of it without overlap; unused parameters' buckets)
         if self.overlap:
             torch.cuda.current_stream().wait_stream(self._comm_stream)
@@ -167,16 +227,72 @@ class DistributedDataParallel(nn.Module):
         for b in self._buckets:
             b.pending = b.nparams
 
+    # ------------------------------------------------------------------ sharded optimizer: parameter all-gather
+    def _make_shard_sync(self, buf):
+        def sync(k):
+            b = buf._shard_buckets[k]
+            if not self.overlap:
+                self.comm.allgather_(buf.data, offset=b.offset, numel=b.numel)
+                return
+            ev = torch.cuda.Event()
+            ev.record(torch.cuda.current_stream())
+            self._comm_stream.wait_event(ev)
+            with torch.cuda.stream(self._comm_stream):
+                self.comm.allgather_(buf.data, offset=b.offset, numel=b.numel,
+                                     max_blocks=self._overlap_blocks if self.overlap_param_sync else 0)
+                b.ag_event.record(self._comm_stream)
+            if self.overlap_param_sync:
+                self._ag_pending[b.key] = b.ag_event
+            elif k + 1 == len(buf._shard_buckets):
+                # every later reader of the parameters is ordered behind the gathers (they still ran under the AdamW
+                # launches of the buckets that followed them)
+                torch.cuda.current_stream().wait_stream(self._comm_stream)
+        return sync
+
+    def _make_param_gate(self, buf):
+        def gate(offset):
+            """Called by code that reads a parameter of this buffer without going through its module's forward."""
+            if not self._ag_pending:
+                return
+            for b in buf._shard_buckets:
+                if b.offset <= offset < b.offset + b.numel:
+                    ev = self._ag_pending.pop(b.key, None)
+                    if ev is not None:
+                        torch.cuda.current_stream().wait_event(ev)
+                    return
+        return gate
+
+    def _gate_module(self, mod, args):
+        if not self._ag_pending:
+            return
+        cur = None
+        for k in self._mod_buckets.get(id(mod), ()):
+            ev = self._ag_pending.pop(k, None)
+            if ev is not None:
+                cur = cur or torch.cuda.current_stream()
+                cur.wait_event(ev)
+
+    def wait_parameters(self):
+        """Orders the current stream behind every parameter all-gather still in flight (sharded optimizer with
+        overlap_param_sync). forward() ends with it, so backward passes and anything after them are safe; call it
+        yourself before reading parameters right after optimizer.step() (state_dict() does)."""
+        if self._ag_pending:
+            cur = torch.cuda.current_stream()
+            for ev in self._ag_pending.values():
+                cur.wait_event(ev)
+            self._ag_pending.clear()
+
     # ------------------------------------------------------------------ nn.Module surface
     def forward(self, *args, **kwargs):
         self.forward_prepare()
-        return self.module(*args, **kwargs)
+        out = self.module(*args, **kwargs)
+        self.wait_parameters()
+        return out
 
     def forward_prepare(self):
-        """Forward-side bookkeeping (gradient views in place, stale reductions forgotten). forward() calls it; call it
-        yourself only when you drive `self.module` piecewise (e.g. its feature extractor + a fused loss)."""
+        """Forward-side bookkeeping (stale reductions forgotten). forward() calls it; call it yourself only when you
+        drive `self.module` piecewise (e.g. its feature extractor + a fused loss)."""
         for buf in self.flat_buffers:
-            buf.ensure_grads()
             buf.reduced_sumsq = None
 
     @contextlib.contextmanager
@@ -192,6 +308,7 @@ class DistributedDataParallel(nn.Module):
 
     def state_dict(self, *args, **kwargs):
         # same key layout as torch DDP: entries are prefixed with "module."
+        self.wait_parameters()
         return super().state_dict(*args, **kwargs)
 
     def close(self):

@@ -27,7 +27,6 @@ class FlatBuffer:
             self.offsets.append(off)
             off += (p.numel() + ALIGN - 1) // ALIGN * ALIGN
         self.numel = (off + TOTAL_MULTIPLE - 1) // TOTAL_MULTIPLE * TOTAL_MULTIPLE
-        self.shard_range = None      # (begin, end) when a data-parallel wrapper shards the optimizer over ranks
         self.comm = None
         alloc = alloc or (lambda n, dt, dev: torch.zeros(n, dtype=dt, device=dev))
         self.data = alloc(self.numel, dtype, device)
@@ -41,13 +40,23 @@ class FlatBuffer:
                 p.data = view
                 p._b2_flat = (self, o)
         self._views = None
-        self.install_grads()
+        self._index = {id(p): i for i, p in enumerate(self.params)}
+        for i, p in enumerate(self.params):
+            if p.grad is not None:             # a gradient that already exists moves into the buffer; none stays none
+                self.grad_view(i).copy_(p.grad)
+                p.grad = self.grad_view(i)
+        for p in self.params:
+            # registered before any wrapper's / optimizer's own hooks: by the time those run, the gradient is in place
+            p.register_post_accumulate_grad_hook(self._land)
         # set by clip_grad_norm_ when an attached optimizer will apply the coefficient inside its kernel
         self.pending_coef = None
         self.optimizer_attached = False
         # exp_avg / exp_avg_sq, created by the optimizer
         self.exp_avg = None
         self.exp_avg_sq = None
+        # [(begin, end, state_offset)] element ranges this rank updates when a data-parallel wrapper shards the optimizer
+        self.shards = None
+        self.after_shard_update = None       # wrapper's callback: (shard index) -> all-gather of that range
 
     def grad_view(self, i):
         """The slice of the flat gradient buffer that is parameter i's .grad (one persistent tensor object per parameter:
@@ -56,9 +65,29 @@ class FlatBuffer:
             self._views = [self.grad[o:o + p.numel()].view(p.shape) for p, o in zip(self.params, self.offsets)]
         return self._views[i]
 
+    def _land(self, p):
+        """Post-accumulate-grad hook. After `zero_grad(set_to_none=True)` (ours, the model's, HF Trainer's) a parameter
+        has no .grad, so autograd hands over the freshly computed gradient tensor instead of adding it to something; here
+        that tensor is copied into the parameter's slice of the flat buffer — one read and one write — and released.
+        (Zero-filling the buffer up front and letting autograd add into it costs a fill plus a read-modify-write: four
+        passes over the gradients instead of two.) Later micro-batches of an accumulation find .grad already pointing
+        into the buffer and autograd adds in place."""
+        i = self._index.get(id(p))
+        if i is None:                          # a copy of one of our parameters that inherited the hook: not ours
+            return
+        want = self.grad_view(i)
+        g = p.grad
+        if g is want:
+            return
+        if g is not None and g.data_ptr() != want.data_ptr():
+            want.copy_(g)
+        p.grad = want
+
     def install_grads(self):
-        """(Re-)point every parameter's .grad at its slice of the flat gradient buffer. A .grad that autograd
-        allocated on its own since (after a zero_grad(set_to_none=True) issued elsewhere) is copied in first."""
+        """Make every parameter's .grad its slice of the flat gradient buffer, as the kernels that run over the whole
+        buffer (sum of squares, all-reduce, AdamW) expect: a gradient that lives elsewhere (assigned by hand, or produced
+        before the buffer existed) is copied in; a parameter WITHOUT a gradient gets a zeroed slice (it contributes
+        nothing to the norm; the optimizer skips it, see AdamW._table_for)."""
         moved = 0
         self.grad_view(0) if self.params else None
         for p, want in zip(self.params, self._views or ()):
@@ -66,6 +95,7 @@ class FlatBuffer:
             if g is want:
                 continue
             if g is None:
+                want.zero_()
                 p.grad = want
             elif g.data_ptr() != want.data_ptr():
                 want.copy_(g)
@@ -76,21 +106,15 @@ class FlatBuffer:
         return moved
 
     def ensure_grads(self):
-        """Before a forward/backward pass: if someone dropped gradients (a foreign `zero_grad(set_to_none=True)`, e.g.
-        HF Trainer's `model.zero_grad()`), hand autograd zero-filled views of the flat buffer again so that it accumulates
-        in place instead of allocating (and later copying) 100+ separate tensors."""
-        missing = [i for i, p in enumerate(self.params) if p.grad is None]
-        if not missing:
-            return
-        if len(missing) == len(self.params):
-            self.grad.zero_()
-        else:
-            for i in missing:
-                self.grad_view(i).zero_()
-        self.install_grads()
+        """Kept for callers of the round-1 API: gradients dropped by a `zero_grad(set_to_none=True)` no longer need to be
+        re-installed before a backward pass — `_land` moves each one into the buffer as it is produced."""
+        return
 
     def zero_grad(self):
-        self.grad.zero_()
+        """`optimizer.zero_grad(set_to_none=True)` (ref: ray-jobs/pytorch_llm_ray.py:273): the gradients are dropped, as
+        in torch — the flat buffer is NOT cleared; each slice is overwritten when its gradient lands."""
+        for p in self.params:
+            p.grad = None
         self.pending_coef = None
 
 

@@ -14,7 +14,7 @@ import torch.nn as nn
 
 from . import ops
 from ._lib import B2Error
-from .flat import buffers_of
+from .flat import flat_of
 
 DEFAULT_CHUNK_ROWS = 8192
 # Keep the forward's bf16 logits for the backward when they fit one chunk (B2_KEEP_LOGITS=0: always recompute them;
@@ -89,13 +89,13 @@ class CrossEntropyLoss(nn.Module):
 class _LMHeadCEFn(torch.autograd.Function):
     @staticmethod
     def forward(ctx, hidden, weight, bias, labels, shift_T, ignore_index, reduction, num_items, round_bf16, chunk_rows,
-                check_labels=False):
+                check_labels=False, weight_shared=False):
         H = hidden if hidden.stride(-1) == 1 else hidden.contiguous()
         bias32 = None if bias is None else bias.detach().to(torch.float32).contiguous()
         # One chunk of rows and a gradient wanted: let the forward leave its bf16 logits in the buffer the backward would
         # otherwise fill by a second pass over the tensor cores; the backward then rewrites them in place (HBM-bound).
         N, V = H.shape[0], weight.shape[0]
-        ldd = (V + 7) // 8 * 8
+        ldd = (V + 63) // 64 * 64          # row pitch: a multiple of 128 bytes
         kept = None
         if (_KEEP_LOGITS and round_bf16 and 0 < N <= chunk_rows and any(ctx.needs_input_grad[:3])
                 and N * ldd * 2 <= _KEEP_LOGITS_MAX_BYTES):
@@ -109,6 +109,9 @@ class _LMHeadCEFn(torch.autograd.Function):
         ctx.bias32, ctx.has_bias = bias32, bias is not None
         ctx.bias_dtype = None if bias is None else bias.dtype
         ctx.cfg = (shift_T, ignore_index, reduction, num_items, round_bf16, chunk_rows)
+        # where the weight's gradient can be written without passing through a fresh [V, D] tensor (see backward)
+        ctx.w_param = weight if (flat_of(weight) is not None and weight.dtype == torch.bfloat16) else None
+        ctx.w_shared = bool(weight_shared)
         ctx.result = r
         return _pick_loss(r, reduction, num_items).clone()
 
@@ -119,7 +122,7 @@ class _LMHeadCEFn(torch.autograd.Function):
         N, D = H.shape
         V = W.shape[0]
         gs = _gscale(grad_out, ctx.result, reduction, num_items)
-        ldd = (V + 7) // 8 * 8
+        ldd = (V + 63) // 64 * 64          # row pitch: a multiple of 128 bytes
         chunk = min(N, chunk_rows)
         kept, ctx.kept = ctx.kept, None
         if kept is None and getattr(ctx, "kept_used", False):
@@ -131,10 +134,31 @@ class _LMHeadCEFn(torch.autograd.Function):
         dH = torch.empty(N, D, dtype=torch.bfloat16, device=H.device) if need_dH else None
         n_chunks = (N + chunk - 1) // chunk
         dW = None
+        # The weight lives in a flat buffer (b200_train.AdamW / prepare_model): its gradient goes STRAIGHT into the
+        # parameter's slice of the flat gradient buffer instead of a fresh [V, D] tensor that autograd would then add or
+        # copy there (two to five extra passes over a 77 MB - 1 GB matrix).
+        #  * weight shared with the input embedding (GPT-2, Llama-3.2-1B; ref: fine_tune_llama_ray.py:230-241 loads such
+        #    models): the GEMM writes (first micro-batch) or accumulates (later ones) into the slice, `.grad` is pointed
+        #    at it, and autograd gets no gradient from here — the embedding's own gradient is then added IN PLACE by
+        #    AccumulateGrad, which also fires the parameter's hooks (bucket ready, optimizer bookkeeping).
+        #  * weight used here only: while the parameter has no gradient yet, the GEMM writes into the slice and autograd
+        #    is handed a fresh alias of it, which AccumulateGrad adopts without a copy; once a gradient exists (later
+        #    micro-batches) the ordinary path runs.
+        direct = None
+        if need_dW and ctx.w_param is not None and W.shape == ctx.w_param.shape:
+            f = flat_of(ctx.w_param)
+            if f is not None:
+                view = f[0].grad_view(f[0]._index[id(ctx.w_param)])
+                have = ctx.w_param.grad is not None and ctx.w_param.grad.data_ptr() == view.data_ptr()
+                if ctx.w_shared or not have:
+                    direct = (view, have)
         if need_dW:
             # one chunk: write bf16 directly; several: accumulate in fp32 and round once at the end, like the
             # single fp32-accumulated GEMM of the reference's autograd
-            dW = torch.empty(V, D, dtype=torch.bfloat16 if n_chunks == 1 else torch.float32, device=H.device)
+            if direct is not None and n_chunks == 1:
+                dW = direct[0]
+            else:
+                dW = torch.empty(V, D, dtype=torch.bfloat16 if n_chunks == 1 else torch.float32, device=H.device)
         db = torch.zeros(V, dtype=torch.float32, device=H.device) if ctx.has_bias else None
         for c in range(n_chunks):
             r0 = c * chunk
@@ -147,18 +171,32 @@ class _LMHeadCEFn(torch.autograd.Function):
             if need_dH:     # dH[rows, D] = dL[rows, V] @ W[V, D]      (B = W read MN-major)
                 ops.gemm_bf16(dl, W, dH[r0:r0 + rows], rows, D, V, a_mn_major=False, b_mn_major=True)
             if need_dW:     # dW[V, D] += dL^T[V, rows] @ H[rows, D]   (A = dL and B = H both read MN-major)
-                ops.gemm_bf16(dl, H[r0:r0 + rows], dW, V, D, rows, a_mn_major=True, b_mn_major=True, accumulate=c > 0)
+                ops.gemm_bf16(dl, H[r0:r0 + rows], dW, V, D, rows, a_mn_major=True, b_mn_major=True,
+                              accumulate=c > 0 or (direct is not None and dW is direct[0] and direct[1]))
             if db is not None:
                 db += dl[:rows, :V].sum(dim=0, dtype=torch.float32)
-        if dW is not None and dW.dtype != W.dtype:
+        if direct is not None:
+            view, have = direct
+            if dW is not view:                       # several chunks: the fp32 sum is rounded once, into the slice
+                if have:
+                    view.add_(dW)
+                else:
+                    view.copy_(dW)
+            if ctx.w_shared:
+                ctx.w_param.grad = view
+                dW = None
+            else:
+                dW = view.view(view.shape)           # a fresh alias nobody else holds: AccumulateGrad keeps it as .grad
+        elif dW is not None and dW.dtype != W.dtype:
             dW = dW.to(W.dtype)
         if db is not None:
             db = db.to(ctx.bias_dtype)
-        return dH, dW, db, None, None, None, None, None, None, None, None
+        return dH, dW, db, None, None, None, None, None, None, None, None, None
 
 
 def fused_lm_head_ce(hidden, weight, labels, bias=None, *, shift=True, ignore_index=-100, reduction="mean",
-                     num_items_in_batch=None, round_logits_bf16=True, chunk_rows=DEFAULT_CHUNK_ROWS, check_labels=False):
+                     num_items_in_batch=None, round_logits_bf16=True, chunk_rows=DEFAULT_CHUNK_ROWS, check_labels=False,
+                     weight_shared=False):
     """loss = CE(hidden @ weight.T (+bias), labels) without the fp32 [N, V] logits / log-probability tensors of the stock path
     (at most a bf16 copy of the logits lives from this forward to its backward, see _KEEP_LOGITS above).
 
@@ -166,7 +204,9 @@ def fused_lm_head_ce(hidden, weight, labels, bias=None, *, shift=True, ignore_in
     (row t is scored against labels[t+1], the last position ignored) exactly as HF's ForCausalLMLoss; shift=False
     expects pre-shifted labels (the reference's TextDataset, ref: ray-jobs/pytorch_llm_ray.py:116-119).
     num_items_in_batch: HF gradient-accumulation normaliser — the loss is sum / num_items_in_batch.
-    check_labels=True raises IndexError on an out-of-range label like torch (one host sync); otherwise the loss is NaN."""
+    check_labels=True raises IndexError on an out-of-range label like torch (one host sync); otherwise the loss is NaN.
+    weight_shared=True promises that `weight` ALSO receives a gradient from elsewhere in the same graph (a tied input
+    embedding): the head's share is then accumulated directly into the parameter's flat gradient slice (see backward)."""
     if hidden.dtype != torch.bfloat16 or weight.dtype != torch.bfloat16:
         raise B2Error("fused_lm_head_ce takes bfloat16 hidden states and weight (use CrossEntropyLoss for fp32 logits)")
     T = hidden.shape[-2] if hidden.dim() >= 2 else 1
@@ -175,24 +215,32 @@ def fused_lm_head_ce(hidden, weight, labels, bias=None, *, shift=True, ignore_in
     if y.device != H2.device:
         y = y.to(H2.device)
     return _LMHeadCEFn.apply(H2, weight, bias, y, T if shift else 0, ignore_index, reduction, num_items_in_batch,
-                             round_logits_bf16, chunk_rows, check_labels)
+                             round_logits_bf16, chunk_rows, check_labels, weight_shared)
 
 
 class FusedLMHeadCE(nn.Module):
     """Module form: owns nothing, borrows the LM head's weight (tied weights keep working)."""
 
     def __init__(self, lm_head, shift=True, ignore_index=-100, reduction="mean", round_logits_bf16=True,
-                 chunk_rows=DEFAULT_CHUNK_ROWS):
+                 chunk_rows=DEFAULT_CHUNK_ROWS, weight_shared=False):
         super().__init__()
         self.lm_head = lm_head
+        self.weight_shared = weight_shared
         self.shift, self.ignore_index, self.reduction = shift, ignore_index, reduction
         self.round_logits_bf16, self.chunk_rows = round_logits_bf16, chunk_rows
 
-    def forward(self, hidden, labels, num_items_in_batch=None):
+    def forward(self, hidden, labels, num_items_in_batch=None, weight_shared=None):
+        # The head's weight is read here without going through lm_head.forward: if a data-parallel wrapper is still
+        # all-gathering updated parameters under this forward pass, wait for the range that holds it.
+        f = flat_of(self.lm_head.weight)
+        gate = getattr(f[0], "param_gate", None) if f is not None else None
+        if gate is not None:
+            gate(f[1])
         return fused_lm_head_ce(hidden, self.lm_head.weight, labels, getattr(self.lm_head, "bias", None),
                                 shift=self.shift, ignore_index=self.ignore_index, reduction=self.reduction,
                                 num_items_in_batch=num_items_in_batch, round_logits_bf16=self.round_logits_bf16,
-                                chunk_rows=self.chunk_rows)
+                                chunk_rows=self.chunk_rows,
+                                weight_shared=self.weight_shared if weight_shared is None else weight_shared)
 
 
 def patch_causal_lm(model, chunk_rows=DEFAULT_CHUNK_ROWS):
@@ -205,6 +253,8 @@ def patch_causal_lm(model, chunk_rows=DEFAULT_CHUNK_ROWS):
     backbone = model.base_model
     if head is None or backbone is model:
         raise B2Error("patch_causal_lm: model has no separate backbone / output embedding")
+    emb = model.get_input_embeddings()
+    tied = emb is not None and getattr(emb, "weight", None) is head.weight
     fused = FusedLMHeadCE(head, shift=True, chunk_rows=chunk_rows)
     orig_forward = model.forward
 
@@ -215,18 +265,12 @@ def patch_causal_lm(model, chunk_rows=DEFAULT_CHUNK_ROWS):
             return orig_forward(input_ids=input_ids, labels=labels, **kw)
         kw.pop("return_dict", None)
         kw.pop("logits_to_keep", None)
-        if torch.is_grad_enabled():
-            # parameters that live in a flat buffer (b200_train.AdamW / prepare_model): keep autograd accumulating into
-            # it even if the caller dropped the gradients with a plain model.zero_grad() (HF Trainer does, every step)
-            bufs = model.__dict__.get("_b2_flat_cache")
-            if not bufs:                               # discovered once the optimizer / prepare_model has flattened them
-                bufs = buffers_of(model.parameters())[0]
-                model.__dict__["_b2_flat_cache"] = bufs
-            for buf in bufs:
-                buf.ensure_grads()
         out = backbone(input_ids=input_ids, **kw)
         hidden = out[0]
-        loss = fused(hidden, labels, num_items_in_batch=num_items_in_batch)
+        # tied head: the embedding lookup of THIS forward also back-propagates into the weight (only when token ids, not
+        # ready-made embeddings, came in)
+        loss = fused(hidden, labels, num_items_in_batch=num_items_in_batch,
+                     weight_shared=tied and input_ids is not None and emb.weight.requires_grad)
         return CausalLMOutputWithPast(loss=loss, logits=None, past_key_values=getattr(out, "past_key_values", None),
                                       hidden_states=getattr(out, "hidden_states", None),
                                       attentions=getattr(out, "attentions", None))

@@ -64,10 +64,10 @@ class AdamW(torch.optim.Optimizer):
         self._share_steps()
         for buf in self._buffers:
             sdt = self._state_dtype or buf.dtype      # torch: zeros_like(p) -> state dtype = param dtype
-            lo, hi = buf.shard_range or (0, buf.numel)
-            if buf.exp_avg is None:                   # sharded: state exists for this rank's slice only
-                buf.exp_avg = torch.zeros(hi - lo, dtype=sdt, device=buf.device)
-                buf.exp_avg_sq = torch.zeros(hi - lo, dtype=sdt, device=buf.device)
+            if buf.exp_avg is None:                   # sharded: state exists for this rank's slices only
+                n_state = buf.numel if buf.shards is None else sum(hi - lo for lo, hi, _ in buf.shards)
+                buf.exp_avg = torch.zeros(max(n_state, 1), dtype=sdt, device=buf.device)[:n_state]
+                buf.exp_avg_sq = torch.zeros(max(n_state, 1), dtype=sdt, device=buf.device)[:n_state]
             table = torch.full((buf.numel // 64,), 255, dtype=torch.uint8)
             for p, o in zip(buf.params, buf.offsets):
                 if id(p) in gid:
@@ -84,7 +84,7 @@ class AdamW(torch.optim.Optimizer):
                 if id(p) not in gid:
                     continue
                 st = self.state[p]
-                if buf.shard_range is None:
+                if buf.shards is None:
                     # views into the flat state: state_dict() keeps torch's per-parameter layout
                     st["exp_avg"] = buf.exp_avg[o:o + p.numel()].view(p.shape)
                     st["exp_avg_sq"] = buf.exp_avg_sq[o:o + p.numel()].view(p.shape)
@@ -142,14 +142,19 @@ class AdamW(torch.optim.Optimizer):
 
     # ------------------------------------------------------------------ torch.optim.Optimizer surface
     def zero_grad(self, set_to_none=True):
-        """ref :273 calls zero_grad(set_to_none=True). The gradients live in a persistent flat buffer that the
-        kernels (and the peer-memory all-reduce) address directly, so they are zero-filled in place rather than
-        dropped; a backward pass accumulates into zeros, which gives the same values as into None."""
+        """ref :273 calls zero_grad(set_to_none=True): the gradients are dropped, as in torch. The next backward pass
+        hands each freshly computed gradient to the flat buffer's hook, which copies it into place (flat.FlatBuffer._land)
+        — the flat gradient buffer itself is neither cleared nor re-allocated. set_to_none=False zero-fills it instead and
+        keeps the `.grad` views."""
         if self._buffers is None:
             return super().zero_grad(set_to_none=set_to_none)
         for buf in self._buffers:
-            buf.zero_grad()
-            buf.install_grads()
+            if set_to_none:
+                buf.zero_grad()
+            else:
+                buf.grad.zero_()
+                buf.pending_coef = None
+                buf.install_grads()
 
     @torch.no_grad()
     def step(self, closure=None):
@@ -170,34 +175,40 @@ class AdamW(torch.optim.Optimizer):
                               step=int(t.item())))
         for buf in self._buffers:
             table = self._table_for(buf)
-            if buf.shard_range is None:
+            if buf.shards is None:
                 ops.adamw_grouped_(buf.data, buf.grad, buf.exp_avg, buf.exp_avg_sq, table, hyper,
                                    gscale=buf.pending_coef)
             else:
-                # this rank's slice only (its gradient slice is the one the reduce-scatter completed), then the updated
-                # slice is pushed to every peer's parameter buffer
-                lo, hi = buf.shard_range
-                ops.adamw_grouped_(buf.data[lo:hi], buf.grad[lo:hi], buf.exp_avg, buf.exp_avg_sq,
-                                   table[lo // 64:hi // 64], hyper, gscale=buf.pending_coef)
-                buf.comm.allgather_(buf.data)
+                # this rank's slices only (the ones the reduce-scatter completed), front of the buffer first; after each
+                # one the wrapper pushes that range of the updated parameters to every peer (on its side stream)
+                for k, (lo, hi, so) in enumerate(buf.shards):
+                    if hi > lo:
+                        ops.adamw_grouped_(buf.data[lo:hi], buf.grad[lo:hi], buf.exp_avg[so:so + hi - lo],
+                                           buf.exp_avg_sq[so:so + hi - lo], table[lo // 64:hi // 64], hyper,
+                                           gscale=buf.pending_coef)
+                    if buf.after_shard_update is not None:
+                        buf.after_shard_update(k)
             buf.pending_coef = None
         self._fired.clear()
         return loss
 
     def _gathered_state(self, buf):
-        """Full-length exp_avg / exp_avg_sq of a sharded buffer (checkpoint path only; NCCL all-gather)."""
+        """Full-length exp_avg / exp_avg_sq of a sharded buffer (checkpoint path only; one NCCL all-reduce each: every
+        element is owned by exactly one rank, the others contribute zeros)."""
         import torch.distributed as dist
         full = []
         for shard in (buf.exp_avg, buf.exp_avg_sq):
-            out = torch.empty(buf.numel, dtype=shard.dtype, device=shard.device)
-            dist.all_gather_into_tensor(out, shard.contiguous(), group=buf.comm.group)
+            out = torch.zeros(buf.numel, dtype=shard.dtype, device=shard.device)
+            for lo, hi, so in buf.shards:
+                out[lo:hi] = shard[so:so + hi - lo]
+            dist.all_reduce(out, group=buf.comm.group)
             full.append(out)
         return full
 
     def state_dict(self):
         """torch's layout (`step`, `exp_avg`, `exp_avg_sq` per parameter, ref: pytorch_llm_ray.py:302) even when the
         state is sharded over ranks: the shards are gathered for the occasion. Collective: call it on every rank."""
-        sharded = [b for b in (self._buffers or []) if b.shard_range is not None]
+        sharded = [b for b in (self._buffers or []) if b.shards is not None]
         for buf in sharded:
             m, v = self._gathered_state(buf)
             for p, o in zip(buf.params, buf.offsets):
@@ -225,16 +236,17 @@ class AdamW(torch.optim.Optimizer):
             return
         # re-home the loaded tensors into the flat state so the kernels see them
         for buf in self._buffers:
-            lo, hi = buf.shard_range or (0, buf.numel)
+            segs = buf.shards if buf.shards is not None else [(0, buf.numel, 0)]
             for p, o in zip(buf.params, buf.offsets):
                 st = self.state.get(p)
                 if not st or "exp_avg" not in st:
                     continue
                 for key, flat in (("exp_avg", buf.exp_avg), ("exp_avg_sq", buf.exp_avg_sq)):
-                    a, b = max(o, lo), min(o + p.numel(), hi)          # part of this parameter that lives in our state
-                    if a < b:
-                        flat[a - lo:b - lo].copy_(st[key].reshape(-1)[a - o:b - o])
-                    if buf.shard_range is None:
+                    for lo, hi, so in segs:
+                        a, b = max(o, lo), min(o + p.numel(), hi)      # part of this parameter that lives in our state
+                        if a < b:
+                            flat[so + a - lo:so + b - lo].copy_(st[key].reshape(-1)[a - o:b - o])
+                    if buf.shards is None:
                         st[key] = flat[o:o + p.numel()].view(p.shape)
                     else:
                         st.pop(key)

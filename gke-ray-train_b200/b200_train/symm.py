@@ -182,32 +182,45 @@ class PeerComm:
              ctypes.byref(b), ctypes.byref(e))
         return b.value, e.value
 
-    def allreduce_(self, t, scale=None, want_sumsq=False, scatter_only=False, offset=0, numel=None, max_blocks=0):
+    def allreduce_(self, t, scale=None, want_sumsq=False, scatter_only=False, offset=0, numel=None, max_blocks=0,
+                   sumsq_out=None):
         """In-place mean (scale = 1/world by default) over ranks of elements [offset, offset+numel) of the flat
-        symmetric tensor `t`. want_sumsq: False / True (restart the sum-of-squares slots) / 2 (keep adding to them)."""
+        symmetric tensor `t`. want_sumsq: False / True (restart the sum-of-squares slots) / 2 (keep adding to them).
+        sumsq_out: fp32 device tensor of `world` elements that the kernel fills with the completed slots as its last act.
+        scatter_only: only this rank's slice of the range (see slice_bounds) is reduced, and it stays local."""
         sb, off = self._symm_of(t)
         self.epoch += 1
         numel = t.numel() - offset if numel is None else numel
         sc = float(1.0 / self.world if scale is None else scale)
         mc = getattr(sb, "mc_ptr", None)
+        if sumsq_out is not None and (sumsq_out.dtype != torch.float32 or sumsq_out.numel() < self.world
+                                      or not sumsq_out.is_contiguous()):
+            raise B2Error("sumsq_out must be a contiguous float32 tensor with one element per rank")
+        so = None if sumsq_out is None else sumsq_out.data_ptr()
         with torch.cuda.device(self.device):
             if mc and self.use_nvls:
                 call("b2_peer_allreduce_mc", mc + off, sb.ptr_table(off), self._flag_table, self.world, self.rank,
                      int(offset), int(numel), dtype_code(t.dtype), sc, self.epoch, int(want_sumsq),
-                     int(bool(scatter_only)), int(max_blocks), stream_ptr())
+                     int(bool(scatter_only)), int(max_blocks), so, stream_ptr())
             else:
                 call("b2_peer_allreduce", sb.ptr_table(off), self._flag_table, self.world, self.rank, int(offset),
                      int(numel), dtype_code(t.dtype), sc, self.epoch, int(want_sumsq), int(bool(scatter_only)),
-                     int(max_blocks), stream_ptr())
+                     int(max_blocks), so, stream_ptr())
         return self._parts if want_sumsq else None
 
-    def allgather_(self, t):
-        """Pushes this rank's slice of `t` to every peer."""
+    def kernel_name(self, t):
+        """Which reduce kernel allreduce_ launches for `t` ("mc" = in-switch NVLS reduction, "ldst" = peer loads/stores)."""
+        sb, _ = self._symm_of(t)
+        return "mc" if (getattr(sb, "mc_ptr", None) and self.use_nvls) else "ldst"
+
+    def allgather_(self, t, offset=0, numel=None, max_blocks=0):
+        """Pushes this rank's slice of elements [offset, offset+numel) of `t` to every peer."""
         sb, off = self._symm_of(t)
         self.epoch += 1
+        numel = t.numel() - offset if numel is None else numel
         with torch.cuda.device(self.device):
-            call("b2_peer_allgather", sb.ptr_table(off), self._flag_table, self.world, self.rank, 0, t.numel(),
-                 dtype_code(t.dtype), self.epoch, stream_ptr())
+            call("b2_peer_allgather", sb.ptr_table(off), self._flag_table, self.world, self.rank, int(offset), int(numel),
+                 dtype_code(t.dtype), self.epoch, int(max_blocks), stream_ptr())
 
     def close(self):
         for sb in self.buffers:

@@ -269,6 +269,7 @@ def _worker(local_rank, world, port, loop, config, backend, use_gpu, storage_dir
 
 def _run_worker(rank, world, local_rank, loop, config, backend, use_gpu, storage_dir, ckpt_cfg, queue, own_pg):
     global _ctx
+    _ddp._use_gpu = bool(use_gpu)
     if use_gpu:
         _t.cuda.set_device(local_rank % _t.cuda.device_count())
     if own_pg and world > 1 and not dist.is_initialized():
@@ -339,16 +340,26 @@ class TorchTrainer:
         port = _free_port()
         procs = mp.start_processes(_worker, args=(world, port, self.loop, self.config, backend, use_gpu, storage_dir,
                                                   ckpt_cfg, queue), nprocs=world, join=False, start_method="spawn")
+        # Collect one report list per worker, without ever blocking on a worker that can no longer post one (killed by
+        # the OOM killer, a segfault in native code, a failed import in the spawned interpreter): the queue is polled
+        # while the process context is checked; ProcessContext.join raises as soon as any worker has failed.
         results = {}
-        while len(results) < world:
-            rank, reports, err = queue.get()
-            results[rank] = (reports, err)
-            if err:
-                break
         try:
-            procs.join()
-        except Exception as e:  # a worker raised: surface it like Ray's Result.error
+            while len(results) < world:
+                if not queue.empty():
+                    rank, reports, err = queue.get()
+                    results[rank] = (reports, err)
+                    if err:
+                        break
+                elif procs.join(timeout=0.2) and queue.empty():
+                    break                      # every worker has exited and nothing is left to read
+            while not procs.join(timeout=1.0):
+                pass
+        except Exception as e:  # a worker raised or died: surface it like Ray's Result.error
             return Result(metrics=None, error=e, path=storage_dir)
+        missing = [r for r in range(world) if r not in results]
+        if missing:
+            return Result(metrics=None, error=RuntimeError(f"workers {missing} exited without reporting"), path=storage_dir)
         return _result_from(results.get(0, ([], None))[0], storage_dir)
 
     def _fit_with_ray(self):

@@ -51,10 +51,15 @@ constexpr int A_STAGE_BYTES = BM * BK * 2;            // 16 KiB: this CTA's 128 
 // B per CTA: all 256 columns (32 KiB) when a CTA works alone, its half of them (16 KiB) in a CTA pair
 constexpr int b_stage_bytes(bool pair) { return (pair ? BN / 2 : BN) * BK * 2; }
 constexpr int stage_bytes(bool pair) { return A_STAGE_BYTES + b_stage_bytes(pair); }
-constexpr int stages_for(bool pair) { return pair ? 6 : 4; }                 // 192 KiB of operand ring either way
-constexpr int STAGING_BYTES = 8 * 2 * 32 * 64;        // storing modes: 8 epilogue warps x 2 alternating [32 rows x 64 B] blocks
+// Operand ring: 192 KiB (4 x 48 KiB alone, 6 x 32 KiB in a pair), plus 32 KiB of staging for the storing modes: one 4 KiB
+// [32 rows x 128 B] box per epilogue warp. (Round 2 tried two boxes per warp paid for with one ring stage — 3 / 5 stages:
+// no gain for pairs, a loss for single CTAs; profiles/README.md.)
+constexpr bool mode_has_staging(int mode) { return mode == 2 || mode == 3; }
+constexpr int stages_for(int mode, bool pair) { return pair ? 6 : 4; }
+constexpr int STAGING_BOX_BYTES = 32 * 128;           // [32 rows x 64 bf16]; the narrow form uses two 2 KiB halves of it
+constexpr int STAGING_BYTES = 8 * STAGING_BOX_BYTES;
 constexpr int smem_bytes_for(int mode, bool pair) {  // + 1 KiB slack to reach 1024-byte alignment
-  return stages_for(pair) * stage_bytes(pair) + 1024 + (mode == 2 || mode == 3 ? STAGING_BYTES : 0);
+  return stages_for(mode, pair) * stage_bytes(pair) + 1024 + (mode_has_staging(mode) ? STAGING_BYTES : 0);
 }
 constexpr int BOX_MN_BYTES = 64 * BK * 2;             // one MN-major TMA box: 64 K-rows x 128 B
 constexpr uint32_t TMEM_COLS = 512;
@@ -82,6 +87,8 @@ struct Params {
   const float* lse; const float* gscale; __nv_bfloat16* dlogits; long long ldd;
   int store_wide;                    // storing modes: 1 = one [32 x 64] TMA store per two chunks, 0 = one [32 x 32] per chunk
   int debug_store;                   // measurement aid (B2_DEBUG_STORE): 1 = stage the tile but issue no TMA store, 2 = drop it
+  int store_direct;                  // storing modes: 1 = each thread writes its 64-byte row segment straight to global memory
+                                     // (no shared-memory staging, no TMA store); needs p.dlogits / p.ldd
 };
 
 __device__ __forceinline__ long long label_at(const Params& p, long long i) {
@@ -122,7 +129,7 @@ template <int MODE, int A_MN, int B_MN, bool PAIR>
 __global__ void __launch_bounds__(NUM_THREADS, 1)
 umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
             const __grid_constant__ CUtensorMap tmD, const Params p) {
-  constexpr int STAGES = stages_for(PAIR);
+  constexpr int STAGES = stages_for(MODE, PAIR);
   constexpr int NC = PAIR ? 2 : 1;
   constexpr int STAGE_BYTES = stage_bytes(PAIR);
   constexpr int BN_CTA = BN / NC;                   // columns of B this CTA keeps in shared memory
@@ -295,9 +302,11 @@ umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
             // 64B-swizzled) and one lane hands it to the TMA engine (coalesced store, clipped at the matrix edge by the
             // tensor map). Two blocks per warp alternate; nothing here synchronises across warps.
             // (store_wide: one [32 x 64] block, 4 KiB, 128B-swizzled, filled by two consecutive chunks and stored once.)
-            if (p.store_wide) {
+            if (p.store_direct) {
+              // nothing staged: nothing to wait for
+            } else if (p.store_wide) {
               if ((cc & 1) == 0) {
-                if (lane_elect) bulk_wait_read_all();  // this warp's previous store has drained the block
+                if (lane_elect) bulk_wait_read_all();  // this warp's previous store has drained the box
                 __syncwarp();
               }
             } else {
@@ -316,8 +325,26 @@ umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
             uint32_t w[16];
 #pragma unroll
             for (int j = 0; j < 32; j += 2) w[j >> 1] = pack_bf16(v[j], v[j + 1]);
+            if (p.store_direct) {
+              // Straight from registers: this thread owns 32 consecutive columns of one row = 64 contiguous bytes = two
+              // whole 32-byte sectors (the row pitch is a multiple of 16 elements, so every segment is sector-aligned).
+              // Vectors that start beyond the pitch are dropped; columns in [N, ldd) are padding nobody reads.
+              if (row_ok) {
+                uint8_t* dst = reinterpret_cast<uint8_t*>(p.dlogits) + ((long long)row * p.ldd + col0) * 2;
+                if (col0 + 32 <= p.ldd) {
+                  st_global_v8_hint(dst, w[0], w[1], w[2], w[3], w[4], w[5], w[6], w[7], store_policy);
+                  st_global_v8_hint(dst + 32, w[8], w[9], w[10], w[11], w[12], w[13], w[14], w[15], store_policy);
+                } else {
+#pragma unroll
+                  for (int k = 0; k < 4; ++k)
+                    if (col0 + 8 * k + 8 <= p.ldd)
+                      *reinterpret_cast<uint4*>(dst + 16 * k) = make_uint4(w[4 * k], w[4 * k + 1], w[4 * k + 2], w[4 * k + 3]);
+                }
+              }
+              return;
+            }
             if (p.store_wide) {
-              uint8_t* box = smem + STAGES * STAGE_BYTES + (warp - 4) * (32 * 128);
+              uint8_t* box = smem + STAGES * STAGE_BYTES + (warp - 4) * STAGING_BOX_BYTES;
               uint8_t* rowp = box + lane * 128;
               const int h = cc & 1;                  // which 64-byte half of the 128-byte row this chunk fills
 #pragma unroll
@@ -333,7 +360,7 @@ umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
               }
               return;
             }
-            uint8_t* box = smem + STAGES * STAGE_BYTES + ((warp - 4) * 2 + (int)(store_seq & 1)) * (32 * 64);
+            uint8_t* box = smem + STAGES * STAGE_BYTES + (warp - 4) * STAGING_BOX_BYTES + (int)(store_seq & 1) * (32 * 64);
             uint8_t* rowp = box + lane * 64;
 #pragma unroll
             for (int k = 0; k < 4; ++k)               // 16-byte chunk k of the 64-byte row, SWIZZLE_64B: k ^ ((row >> 1) & 3)
@@ -479,7 +506,7 @@ umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
         if (z_found) p.zt[row] = zval;
       }
     }
-    if (mode_stores(MODE) && lane_elect) bulk_wait_all();   // this warp's last stores have landed (same lane that issued them)
+    if (mode_stores(MODE) && !p.store_direct && lane_elect) bulk_wait_all();   // this warp's last stores have landed (same lane that issued them)
   }
 
   tc_fence_before();
@@ -645,6 +672,15 @@ int debug_store() {
   static const int v = [] { const char* e = getenv("B2_DEBUG_STORE"); return e == nullptr ? 0 : atoi(e); }();
   return v;
 }
+// B2_STORE_DIRECT=1: the storing epilogues write global memory straight from registers (A/B against the staged TMA stores)
+int store_direct_env() {
+  static const int v = [] { const char* e = getenv("B2_STORE_DIRECT"); return e == nullptr ? -1 : atoi(e); }();
+  return v;
+}
+// direct stores need a 32-byte aligned buffer whose row pitch is a multiple of 16 elements
+bool store_direct_ok(const void* ptr, long long pitch) {
+  return store_direct_env() == 1 && pitch % 16 == 0 && b2_aligned(ptr, 32);
+}
 bool store_wide() {
   static const bool wide = [] { const char* e = getenv("B2_STORE_BOX"); return e == nullptr ? true : atoi(e) == 64; }();
   return wide;
@@ -654,19 +690,21 @@ int make_store_tmap(CUtensorMap* m, const void* ptr, long long cols, long long r
                       : make_tmap(m, ptr, cols, rows, pitch, 32, 32, what, CU_TENSOR_MAP_SWIZZLE_64B);
 }
 
-// CTA pairs (tcgen05 cta_group::2, M = 256 per MMA) for the plain GEMMs (long K, light epilogue); the two cross-entropy
-// kernels, whose epilogues are the heavier side, measured faster with independent CTAs that are not coupled through a
-// shared accumulator hand-off (profiles/README.md). B2_PAIR=0 / B2_PAIR=1 in the environment forces one shape
-// everywhere (A/B measurements).
-bool use_pair(int mode) {
+// CTA pairs (tcgen05 cta_group::2, M = 256 per MMA: each CTA loads half of the B tile, a third less L2 -> SM operand traffic)
+// or independent CTAs. Measured with the warp-uniform issue loops (profiles/README.md, round 2): pairs win for the plain
+// GEMMs, for the forward that stores its logits at every shape, and for both cross-entropy kernels once K >= 1024 (Llama
+// heads: forward 1.38 -> 1.31 ms, d(logits) 1.51 -> 1.33 ms at D = 2048); at K = 768 (GPT-2) independent CTAs are a few
+// percent ahead for the two kernels that do not store. B2_PAIR=0 / B2_PAIR=1 forces one shape everywhere (A/B runs).
+bool use_pair(int mode, int K) {
   static const int forced = [] { const char* e = getenv("B2_PAIR"); return e == nullptr ? -1 : (e[0] != '0'); }();
   if (forced >= 0) return forced != 0;
-  return mode == MODE_GEMM;
+  if (mode == MODE_GEMM || mode == MODE_CE_FWD_KEEP) return true;
+  return K >= 1024;
 }
 // rows of A covered by one work unit
-int rows_per_unit(int mode) { return use_pair(mode) ? 2 * BM : BM; }
+int rows_per_unit(bool pair) { return pair ? 2 * BM : BM; }
 // CTAs (single mode) or CTA pairs (pair mode) that run concurrently
-int num_workers(int mode) { return use_pair(mode) ? num_sms() / 2 : num_sms(); }
+int num_workers(bool pair) { return pair ? num_sms() / 2 : num_sms(); }
 
 template <int MODE, int A_MN, int B_MN, bool PAIR>
 int launch_impl(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& td, const Params& p, cudaStream_t stream) {
@@ -674,7 +712,7 @@ int launch_impl(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap&
   constexpr int SMEM_BYTES = smem_bytes_for(MODE, PAIR);
   B2_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
   const int units = p.num_m_blocks * p.n_splits * p.k_splits;
-  const int workers = units < num_workers(MODE) ? units : num_workers(MODE);
+  const int workers = units < num_workers(PAIR) ? units : num_workers(PAIR);
   cudaLaunchConfig_t cfg{};
   cfg.gridDim = dim3((unsigned)(workers * (PAIR ? 2 : 1)));
   cfg.blockDim = dim3(NUM_THREADS);
@@ -689,9 +727,9 @@ int launch_impl(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap&
 }
 
 template <int MODE, int A_MN, int B_MN>
-int launch(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& td, const Params& p, cudaStream_t stream) {
-  return use_pair(MODE) ? launch_impl<MODE, A_MN, B_MN, true>(ta, tb, td, p, stream)
-                    : launch_impl<MODE, A_MN, B_MN, false>(ta, tb, td, p, stream);
+int launch(bool pair, const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& td, const Params& p, cudaStream_t stream) {
+  return pair ? launch_impl<MODE, A_MN, B_MN, true>(ta, tb, td, p, stream)
+              : launch_impl<MODE, A_MN, B_MN, false>(ta, tb, td, p, stream);
 }
 
 // operand [rows = M or N extent, K] -> tensor map; K-major: memory is [extent, ld] with K contiguous;
@@ -769,24 +807,28 @@ extern "C" int b2_gemm_bf16(const void* A, int a_mn_major, long long lda, const 
   CUtensorMap ta, tb;
   int rc;
   if ((rc = make_operand_tmap(&ta, A, a_mn_major, M, K, lda, BM, "b2_gemm_bf16 A")) != B2_OK) return rc;
-  if ((rc = make_operand_tmap(&tb, B, b_mn_major, N, K, ldb, use_pair(MODE_GEMM) ? BN / 2 : BN, "b2_gemm_bf16 B")) != B2_OK) return rc;
+  const bool pair = use_pair(MODE_GEMM, K);
+  if ((rc = make_operand_tmap(&tb, B, b_mn_major, N, K, ldb, pair ? BN / 2 : BN, "b2_gemm_bf16 B")) != B2_OK) return rc;
   Params p{};
   p.M = M; p.N = N; p.K = K;
-  p.num_m_blocks = (M + rows_per_unit(MODE_GEMM) - 1) / rows_per_unit(MODE_GEMM); p.num_n_blocks = (N + BN - 1) / BN; p.num_k_blocks = (K + BK - 1) / BK;
+  p.num_m_blocks = (M + rows_per_unit(pair) - 1) / rows_per_unit(pair); p.num_n_blocks = (N + BN - 1) / BN; p.num_k_blocks = (K + BK - 1) / BK;
   p.n_splits = p.num_n_blocks;
-  p.n_fastest = p.num_n_blocks <= 8;     // few column blocks: let the CTAs that share an A row-block run side by side
+  // Unit order: the CTAs that run at the same time should share operand tiles through L2. Few column blocks, or a B
+  // operand that fits L2 as a whole (dW at D = 4096: H^T is 33 MB, while one wave of distinct A strips is 150 MB and
+  // was being re-read from HBM once per column block): let the units that share an A row-block run side by side.
+  p.n_fastest = p.num_n_blocks <= 8 || (long long)N * K * 2 <= (48ll << 20);
   p.k_splits = 1;
   if (workspace != nullptr && workspace_bytes >= b2_gemm_workspace_bytes(M, N) && b2_aligned(workspace, 16))
-    p.k_splits = auto_k_splits(p.num_m_blocks * p.num_n_blocks, p.num_k_blocks, num_workers(MODE_GEMM));
+    p.k_splits = auto_k_splits(p.num_m_blocks * p.num_n_blocks, p.num_k_blocks, num_workers(pair));
   p.ws = static_cast<float*>(workspace); p.ldws = ((long long)N + 3) / 4 * 4;
   p.C = C; p.ldc = ldc; p.c_dtype = c_dtype; p.accumulate = accumulate;
   // profiling only: mainloop ceiling without the epilogue stores (=1) or without even reading the accumulator (=2)
   static const int noepi = [] { const char* e = getenv("B2_DEBUG_NOEPI"); return e == nullptr ? 0 : (e[0] == '2' ? 2 : 1); }();
   if (noepi) { p.c_dtype = noepi == 2 ? 98 : 99; p.k_splits = 1; }
-  if (!a_mn_major && !b_mn_major) rc = launch<MODE_GEMM, 0, 0>(ta, tb, ta, p, stream);
-  else if (!a_mn_major && b_mn_major) rc = launch<MODE_GEMM, 0, 1>(ta, tb, ta, p, stream);
-  else if (a_mn_major && !b_mn_major) rc = launch<MODE_GEMM, 1, 0>(ta, tb, ta, p, stream);
-  else rc = launch<MODE_GEMM, 1, 1>(ta, tb, ta, p, stream);
+  if (!a_mn_major && !b_mn_major) rc = launch<MODE_GEMM, 0, 0>(pair, ta, tb, ta, p, stream);
+  else if (!a_mn_major && b_mn_major) rc = launch<MODE_GEMM, 0, 1>(pair, ta, tb, ta, p, stream);
+  else if (a_mn_major && !b_mn_major) rc = launch<MODE_GEMM, 1, 0>(pair, ta, tb, ta, p, stream);
+  else rc = launch<MODE_GEMM, 1, 1>(pair, ta, tb, ta, p, stream);
   if (rc != B2_OK || p.k_splits == 1) return rc;
   const long long total = (long long)M * (p.ldws / 4);
   long long blocks = (total + 255) / 256;
@@ -819,22 +861,24 @@ static int lmhead_ce_fwd_impl(const void* H, long long ldh, const void* W, long 
     CUtensorMap ta, tb;
     int rc;
     if ((rc = make_operand_tmap(&ta, H, 0, N, D, ldh, BM, "b2_lmhead_ce_fwd H")) != B2_OK) return rc;
-    if ((rc = make_operand_tmap(&tb, W, 0, V, D, ldw, use_pair(MODE_CE_FWD) ? BN / 2 : BN, "b2_lmhead_ce_fwd W")) != B2_OK) return rc;
+    const bool pair = use_pair(logits_out == nullptr ? MODE_CE_FWD : MODE_CE_FWD_KEEP, D);
+    if ((rc = make_operand_tmap(&tb, W, 0, V, D, ldw, pair ? BN / 2 : BN, "b2_lmhead_ce_fwd W")) != B2_OK) return rc;
     Params p{};
     p.M = (int)N; p.N = V; p.K = D;
-    p.num_m_blocks = (int)((N + rows_per_unit(MODE_CE_FWD) - 1) / rows_per_unit(MODE_CE_FWD)); p.num_n_blocks = (V + BN - 1) / BN; p.num_k_blocks = (D + BK - 1) / BK;
-    p.n_splits = choose_splits(p.num_m_blocks, p.num_n_blocks, num_workers(MODE_CE_FWD));
+    p.num_m_blocks = (int)((N + rows_per_unit(pair) - 1) / rows_per_unit(pair)); p.num_n_blocks = (V + BN - 1) / BN; p.num_k_blocks = (D + BK - 1) / BK;
+    p.n_splits = choose_splits(p.num_m_blocks, p.num_n_blocks, num_workers(pair));
     p.k_splits = 1; p.n_fastest = 0;
     p.labels = labels; p.shift_T = shift_T; p.ignore_index = ignore_index; p.row0 = 0;
     p.bias = bias; p.round_bf16 = round_logits_bf16;
     p.part = static_cast<float2*>(workspace); p.part_stride = (N + BM - 1) / BM * BM; p.zt = zt;
     if (logits_out == nullptr) {
-      if ((rc = launch<MODE_CE_FWD, 0, 0>(ta, tb, ta, p, stream)) != B2_OK) return rc;
+      if ((rc = launch<MODE_CE_FWD, 0, 0>(pair, ta, tb, ta, p, stream)) != B2_OK) return rc;
     } else {
       CUtensorMap td;
       if ((rc = make_store_tmap(&td, logits_out, V, N, ldl, "b2_lmhead_ce_fwd_keep logits")) != B2_OK) return rc;
       p.store_wide = store_wide(); p.debug_store = debug_store();
-      if ((rc = launch<MODE_CE_FWD_KEEP, 0, 0>(ta, tb, td, p, stream)) != B2_OK) return rc;
+      p.dlogits = static_cast<__nv_bfloat16*>(logits_out); p.ldd = ldl; p.store_direct = store_direct_ok(logits_out, ldl);
+      if ((rc = launch<MODE_CE_FWD_KEEP, 0, 0>(pair, ta, tb, td, p, stream)) != B2_OK) return rc;
     }
     ce_combine_kernel<<<(unsigned)((N + 255) / 256), 256, 0, stream>>>(p.part, p.part_stride, 2 * p.n_splits, N, lse);
     B2_CHECK_CUDA(cudaGetLastError());
@@ -894,16 +938,17 @@ extern "C" int b2_lmhead_ce_bwd_dlogits(const void* H, long long ldh, const void
   CUtensorMap ta, tb;
   int rc;
   if ((rc = make_operand_tmap(&ta, H, 0, rows, D, ldh, BM, "b2_lmhead_ce_bwd_dlogits H")) != B2_OK) return rc;
-  if ((rc = make_operand_tmap(&tb, W, 0, V, D, ldw, use_pair(MODE_CE_BWD) ? BN / 2 : BN, "b2_lmhead_ce_bwd_dlogits W")) != B2_OK) return rc;
+  const bool pair = use_pair(MODE_CE_BWD, D);
+  if ((rc = make_operand_tmap(&tb, W, 0, V, D, ldw, pair ? BN / 2 : BN, "b2_lmhead_ce_bwd_dlogits W")) != B2_OK) return rc;
   Params p{};
   p.M = (int)rows; p.N = V; p.K = D;
-  p.num_m_blocks = (int)((rows + rows_per_unit(MODE_CE_BWD) - 1) / rows_per_unit(MODE_CE_BWD)); p.num_n_blocks = (V + BN - 1) / BN; p.num_k_blocks = (D + BK - 1) / BK;
+  p.num_m_blocks = (int)((rows + rows_per_unit(pair) - 1) / rows_per_unit(pair)); p.num_n_blocks = (V + BN - 1) / BN; p.num_k_blocks = (D + BK - 1) / BK;
   p.n_splits = p.num_n_blocks; p.k_splits = 1; p.n_fastest = 0;
   p.labels = labels; p.shift_T = shift_T; p.ignore_index = ignore_index; p.row0 = row0;
   p.bias = bias; p.round_bf16 = round_logits_bf16;
   p.lse = lse; p.gscale = gscale_dev; p.dlogits = static_cast<__nv_bfloat16*>(dlogits); p.ldd = ldd;
   CUtensorMap td;
   if ((rc = make_store_tmap(&td, dlogits, V, rows, ldd, "b2_lmhead_ce_bwd_dlogits dlogits")) != B2_OK) return rc;
-  p.store_wide = store_wide(); p.debug_store = debug_store();
-  return launch<MODE_CE_BWD, 0, 0>(ta, tb, td, p, stream);
+  p.store_wide = store_wide(); p.debug_store = debug_store(); p.store_direct = store_direct_ok(dlogits, ldd);
+  return launch<MODE_CE_BWD, 0, 0>(pair, ta, tb, td, p, stream);
 }

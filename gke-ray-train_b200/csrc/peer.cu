@@ -25,7 +25,10 @@
 //   [0..7]   start-barrier arrivals, one word per source rank     [8..15] end-barrier arrivals
 //   [16]     local block ticket (self-resetting)                  [17]    error word (timeout)
 //   [32..63] float sumsq slots: [32 + src_rank]
-#define B2_PEER_FLAG_WORDS 64
+//   [64..383] per-block sum-of-squares partials of the running kernel (added in block order by its last block)
+#define B2_PEER_FLAG_WORDS 384
+#define B2_PEER_PARTIALS 64
+#define B2_PEER_MAX_BLOCKS 320
 
 namespace {
 
@@ -108,6 +111,50 @@ __device__ __forceinline__ void end_barrier(const PeerPtrs& pp, int world, int r
   __syncthreads();
 }
 
+// Tail of the reducing kernels: the sum of squares of this rank's slice, then the end barrier.
+// Each block leaves its partial in the flag block; the block that arrives last adds them IN BLOCK ORDER (double), so the
+// result does not depend on the order in which blocks finish — the norm clip_grad_norm_ returns is reproducible run to
+// run. want_sumsq 1: the slot restarts from this launch's total; 2: the total is added to the slot (next bucket of the
+// same buffer). The finished slot is pushed to every peer before the end-barrier signal, so when the kernel retires all
+// W slots of this rank's flag block are complete; they are then copied to `sumsq_out` (local, W floats) if given.
+__device__ __forceinline__ void finish_reduce(const PeerPtrs& pp, int world, int rank, uint32_t epoch, int want_sumsq,
+                                              float ss, float* red, float* sumsq_out) {
+  __shared__ bool last;
+  uint32_t* mine = pp.flags[rank];
+  if (want_sumsq) {
+    const float b = block_sum(ss, red);
+    if (threadIdx.x == 0) reinterpret_cast<volatile float*>(mine + B2_PEER_PARTIALS)[blockIdx.x] = b;
+  }
+  __threadfence_system();
+  __syncthreads();
+  if (threadIdx.x == 0) last = (atomicAdd(mine + 16, 1u) == gridDim.x - 1);
+  __syncthreads();
+  if (!last) return;
+  __threadfence_system();
+  if (want_sumsq) {
+    if (threadIdx.x == 0) {
+      double tot = 0.0;
+      for (unsigned b = 0; b < gridDim.x; ++b) tot += (double)reinterpret_cast<volatile float*>(mine + B2_PEER_PARTIALS)[b];
+      volatile float* slot = reinterpret_cast<volatile float*>(mine + 32 + rank);
+      *slot = (want_sumsq == 2) ? (float)((double)*slot + tot) : (float)tot;
+      __threadfence_system();
+    }
+    __syncthreads();
+  }
+  if ((int)threadIdx.x < world) {
+    if (want_sumsq && (int)threadIdx.x != rank) {
+      const uint32_t bits = ld_acquire_sys(mine + 32 + rank);
+      asm volatile("st.relaxed.sys.global.u32 [%0], %1;" :: "l"(pp.flags[threadIdx.x] + 32 + rank), "r"(bits) : "memory");
+      __threadfence_system();
+    }
+    st_release_sys(pp.flags[threadIdx.x] + 8 + rank, epoch);
+    wait_flag(mine + 8 + threadIdx.x, epoch, mine + 17);
+    // peer `threadIdx.x` pushed its slot before that signal
+    if (want_sumsq && sumsq_out != nullptr) sumsq_out[threadIdx.x] = *reinterpret_cast<volatile float*>(mine + 32 + threadIdx.x);
+  }
+  if (threadIdx.x == 0) mine[16] = 0u;
+}
+
 template <int DT> struct PeerVec;
 template <> struct PeerVec<B2_F32> {
   static constexpr int kElems = 4;
@@ -133,7 +180,8 @@ template <> struct PeerVec<B2_BF16> {
 // vectors [v0, v1) of 16 bytes belong to this rank
 template <int DT, int WORLD, bool SCATTER_ONLY>
 __global__ void __launch_bounds__(512) peer_allreduce_kernel(const __grid_constant__ PeerPtrs pp, int rank, size_t v0,
-                                                             size_t v1, float scale, uint32_t epoch, int want_sumsq) {
+                                                             size_t v1, float scale, uint32_t epoch, int want_sumsq,
+                                                             float* sumsq_out) {
   using V = PeerVec<DT>;
   __shared__ float red[32];
   start_barrier(pp, WORLD, rank, epoch);
@@ -169,31 +217,7 @@ __global__ void __launch_bounds__(512) peer_allreduce_kernel(const __grid_consta
     }
   }
 
-  if (want_sumsq) {
-    // per-rank partial: block sums are added into the local slot by atomics (order varies run to run at the
-    // level of fp32 rounding of <= grid partials); the finished slot is then pushed to every peer.
-    const float b = block_sum(ss, red);
-    if (threadIdx.x == 0) atomicAdd(reinterpret_cast<float*>(pp.flags[rank] + 32 + rank), b);
-  }
-  // end barrier, with the sumsq slot published by the last block before it signals
-  __shared__ bool last;
-  uint32_t* mine = pp.flags[rank];
-  __threadfence_system();
-  __syncthreads();
-  if (threadIdx.x == 0) last = (atomicAdd(mine + 16, 1u) == gridDim.x - 1);
-  __syncthreads();
-  if (!last) return;
-  __threadfence_system();
-  if (threadIdx.x < WORLD) {
-    if (want_sumsq && (int)threadIdx.x != rank) {
-      const uint32_t bits = ld_acquire_sys(mine + 32 + rank);
-      asm volatile("st.relaxed.sys.global.u32 [%0], %1;" :: "l"(pp.flags[threadIdx.x] + 32 + rank), "r"(bits) : "memory");
-      __threadfence_system();
-    }
-    st_release_sys(pp.flags[threadIdx.x] + 8 + rank, epoch);
-    wait_flag(mine + 8 + threadIdx.x, epoch, mine + 17);
-  }
-  if (threadIdx.x == 0) mine[16] = 0u;
+  finish_reduce(pp, WORLD, rank, epoch, want_sumsq, ss, red, sumsq_out);
 }
 
 template <int WORLD>
@@ -208,10 +232,6 @@ __global__ void __launch_bounds__(512) peer_allgather_kernel(const __grid_consta
       if (k != rank) st_peer(static_cast<uint4*>(pp.buf[k]) + i, v);
   }
   end_barrier(pp, WORLD, rank, epoch);
-}
-
-__global__ void peer_zero_sumsq_kernel(uint32_t* flags) {
-  if (threadIdx.x < 32) flags[32 + threadIdx.x] = 0u;
 }
 
 int fill_ptrs(PeerPtrs& pp, void* const* bufs, uint32_t* const* flags, int world, size_t byte_offset, const char* what) {
@@ -229,8 +249,12 @@ int fill_ptrs(PeerPtrs& pp, void* const* bufs, uint32_t* const* flags, int world
 }
 
 // slice of rank r in 16-byte vectors: contiguous, equal-sized (last one ragged)
-void slice_of(size_t nvec, int world, int rank, size_t& v0, size_t& v1) {
-  const size_t per = (nvec + world - 1) / world;
+// Slices start on 64-element boundaries (4 or 16 vectors... `align_vec` = 64 elements in vectors), the granularity of the
+// AdamW chunk table, so that a sharded optimizer can update exactly the slice it reduced — also for a bucket (a sub-range
+// of the flat buffer) whose length is not a multiple of 64 * world.
+void slice_of(size_t nvec, int world, int rank, size_t align_vec, size_t& v0, size_t& v1) {
+  size_t per = (nvec + world - 1) / world;
+  per = (per + align_vec - 1) / align_vec * align_vec;
   v0 = per * rank < nvec ? per * rank : nvec;
   v1 = v0 + per < nvec ? v0 + per : nvec;
 }
@@ -240,6 +264,7 @@ unsigned peer_grid(size_t nvec_slice, int max_blocks) {
   size_t cap = (size_t)B2_NUM_SMS * 2;           // 2 x 512 threads per SM: enough loads in flight to cover NVLink latency
   if (max_blocks > 0 && (size_t)max_blocks < cap) cap = (size_t)max_blocks;   // overlapped with compute: leave SMs free
   if (blocks > cap) blocks = cap;
+  if (blocks > B2_PEER_MAX_BLOCKS) blocks = B2_PEER_MAX_BLOCKS;     // one sum-of-squares partial per block in the flag block
   if (blocks == 0) blocks = 1;
   return (unsigned)blocks;
 }
@@ -284,7 +309,7 @@ extern "C" int b2_symm_free(void* dptr) {
 // ---- collectives ------------------------------------------------------------------------------------------------
 extern "C" int b2_peer_allreduce(void* const* peer_bufs, uint32_t* const* peer_flags, int world, int rank,
                                  size_t offset_elems, size_t n, int dtype, float scale, unsigned epoch, int want_sumsq,
-                                 int scatter_only, int max_blocks, cudaStream_t stream) {
+                                 int scatter_only, int max_blocks, float* sumsq_out, cudaStream_t stream) {
   B2_REQUIRE(dtype == B2_F32 || dtype == B2_BF16, "b2_peer_allreduce: dtype must be 0 (f32) or 1 (bf16)");
   B2_REQUIRE(rank >= 0 && rank < world, "b2_peer_allreduce: rank %d outside world %d", rank, world);
   const size_t es = b2_dtype_size(dtype), per_vec = 16 / es;
@@ -293,13 +318,12 @@ extern "C" int b2_peer_allreduce(void* const* peer_bufs, uint32_t* const* peer_f
   int rc = fill_ptrs(pp, peer_bufs, peer_flags, world, offset_elems * es, "b2_peer_allreduce");
   if (rc != B2_OK) return rc;
   size_t v0, v1;
-  slice_of(n / per_vec, world, rank, v0, v1);
-  if (want_sumsq == 1) peer_zero_sumsq_kernel<<<1, 32, 0, stream>>>(pp.flags[rank]);   // 2 = keep adding to the slots
+  slice_of(n / per_vec, world, rank, 64 / per_vec, v0, v1);
   const unsigned grid = peer_grid(v1 - v0, max_blocks);
 #define B2_PEER_CASE(DT, W)                                                                                        \
   if (dtype == DT && world == W) {                                                                                 \
-    if (scatter_only) peer_allreduce_kernel<DT, W, true><<<grid, 512, 0, stream>>>(pp, rank, v0, v1, scale, epoch, want_sumsq); \
-    else peer_allreduce_kernel<DT, W, false><<<grid, 512, 0, stream>>>(pp, rank, v0, v1, scale, epoch, want_sumsq);  \
+    if (scatter_only) peer_allreduce_kernel<DT, W, true><<<grid, 512, 0, stream>>>(pp, rank, v0, v1, scale, epoch, want_sumsq, sumsq_out); \
+    else peer_allreduce_kernel<DT, W, false><<<grid, 512, 0, stream>>>(pp, rank, v0, v1, scale, epoch, want_sumsq, sumsq_out);  \
     B2_CHECK_CUDA(cudaGetLastError());                                                                             \
     return B2_OK;                                                                                                  \
   }
@@ -313,7 +337,8 @@ extern "C" int b2_peer_allreduce(void* const* peer_bufs, uint32_t* const* peer_f
 }
 
 extern "C" int b2_peer_allgather(void* const* peer_bufs, uint32_t* const* peer_flags, int world, int rank,
-                                 size_t offset_elems, size_t n, int dtype, unsigned epoch, cudaStream_t stream) {
+                                 size_t offset_elems, size_t n, int dtype, unsigned epoch, int max_blocks,
+                                 cudaStream_t stream) {
   B2_REQUIRE(dtype == B2_F32 || dtype == B2_BF16, "b2_peer_allgather: dtype must be 0 (f32) or 1 (bf16)");
   B2_REQUIRE(rank >= 0 && rank < world, "b2_peer_allgather: rank %d outside world %d", rank, world);
   const size_t es = b2_dtype_size(dtype), per_vec = 16 / es;
@@ -322,8 +347,8 @@ extern "C" int b2_peer_allgather(void* const* peer_bufs, uint32_t* const* peer_f
   int rc = fill_ptrs(pp, peer_bufs, peer_flags, world, offset_elems * es, "b2_peer_allgather");
   if (rc != B2_OK) return rc;
   size_t v0, v1;
-  slice_of(n / per_vec, world, rank, v0, v1);
-  const unsigned grid = peer_grid(v1 - v0, 0);
+  slice_of(n / per_vec, world, rank, 64 / per_vec, v0, v1);
+  const unsigned grid = peer_grid(v1 - v0, max_blocks);
 #define B2_AG_CASE(W)                                                                       \
   if (world == W) {                                                                         \
     peer_allgather_kernel<W><<<grid, 512, 0, stream>>>(pp, rank, v0, v1, epoch);            \
@@ -341,7 +366,7 @@ extern "C" int b2_peer_slice(size_t n, int dtype, int world, int rank, size_t* b
   B2_REQUIRE(begin && end && world >= 1 && rank >= 0 && rank < world, "b2_peer_slice: bad arguments");
   const size_t per_vec = 16 / b2_dtype_size(dtype);
   size_t v0, v1;
-  slice_of(n / per_vec, world, rank, v0, v1);
+  slice_of(n / per_vec, world, rank, 64 / per_vec, v0, v1);
   *begin = v0 * per_vec;
   *end = v1 * per_vec;
   return B2_OK;
@@ -424,7 +449,7 @@ template <> struct McOps<B2_F32> {
 template <int DT, bool SCATTER_ONLY>
 __global__ void __launch_bounds__(512) peer_allreduce_mc_kernel(const __grid_constant__ PeerPtrs pp, void* mc, int world,
                                                                 int rank, size_t v0, size_t v1, float scale,
-                                                                uint32_t epoch, int want_sumsq) {
+                                                                uint32_t epoch, int want_sumsq, float* sumsq_out) {
   using V = PeerVec<DT>;
   __shared__ float red[32];
   start_barrier(pp, world, rank, epoch);
@@ -457,35 +482,14 @@ __global__ void __launch_bounds__(512) peer_allreduce_mc_kernel(const __grid_con
       else McOps<DT>::st(static_cast<uint4*>(mc) + i, out);
     }
   }
-  if (want_sumsq) {
-    const float b = block_sum(ss, red);
-    if (threadIdx.x == 0) atomicAdd(reinterpret_cast<float*>(pp.flags[rank] + 32 + rank), b);
-  }
-  __shared__ bool last;
-  uint32_t* mine = pp.flags[rank];
-  __threadfence_system();
-  __syncthreads();
-  if (threadIdx.x == 0) last = (atomicAdd(mine + 16, 1u) == gridDim.x - 1);
-  __syncthreads();
-  if (!last) return;
-  __threadfence_system();
-  if ((int)threadIdx.x < world) {
-    if (want_sumsq && (int)threadIdx.x != rank) {
-      const uint32_t bits = ld_acquire_sys(mine + 32 + rank);
-      asm volatile("st.relaxed.sys.global.u32 [%0], %1;" :: "l"(pp.flags[threadIdx.x] + 32 + rank), "r"(bits) : "memory");
-      __threadfence_system();
-    }
-    st_release_sys(pp.flags[threadIdx.x] + 8 + rank, epoch);
-    wait_flag(mine + 8 + threadIdx.x, epoch, mine + 17);
-  }
-  if (threadIdx.x == 0) mine[16] = 0u;
+  finish_reduce(pp, world, rank, epoch, want_sumsq, ss, red, sumsq_out);
 }
 
 }  // namespace
 
 extern "C" int b2_peer_allreduce_mc(void* mc_buf, void* const* peer_bufs, uint32_t* const* peer_flags, int world, int rank,
                                     size_t offset_elems, size_t n, int dtype, float scale, unsigned epoch, int want_sumsq,
-                                    int scatter_only, int max_blocks, cudaStream_t stream) {
+                                    int scatter_only, int max_blocks, float* sumsq_out, cudaStream_t stream) {
   B2_REQUIRE(mc_buf, "b2_peer_allreduce_mc: null multicast pointer");
   B2_REQUIRE(dtype == B2_F32 || dtype == B2_BF16, "b2_peer_allreduce_mc: dtype must be 0 (f32) or 1 (bf16)");
   B2_REQUIRE(rank >= 0 && rank < world, "b2_peer_allreduce_mc: rank %d outside world %d", rank, world);
@@ -497,18 +501,17 @@ extern "C" int b2_peer_allreduce_mc(void* mc_buf, void* const* peer_bufs, uint32
   void* mc = static_cast<char*>(mc_buf) + offset_elems * es;
   B2_REQUIRE(b2_aligned(mc, 16), "b2_peer_allreduce_mc: multicast pointer (+offset) must be 16-byte aligned");
   size_t v0, v1;
-  slice_of(n / per_vec, world, rank, v0, v1);
-  if (want_sumsq == 1) peer_zero_sumsq_kernel<<<1, 32, 0, stream>>>(pp.flags[rank]);
+  slice_of(n / per_vec, world, rank, 64 / per_vec, v0, v1);
   // the switch does the adding: a few dozen CTAs keep it busy, more only contend (measured at W = 8: 32 CTAs 842 GB/s,
   // 296 CTAs 800 GB/s on 2 GiB; profiles/README.md)
   const int mc_cap = 32;
   const unsigned grid = peer_grid(v1 - v0, (max_blocks > 0 && max_blocks < mc_cap) ? max_blocks : mc_cap);
   if (dtype == B2_BF16) {
-    if (scatter_only) peer_allreduce_mc_kernel<B2_BF16, true><<<grid, 512, 0, stream>>>(pp, mc, world, rank, v0, v1, scale, epoch, want_sumsq);
-    else peer_allreduce_mc_kernel<B2_BF16, false><<<grid, 512, 0, stream>>>(pp, mc, world, rank, v0, v1, scale, epoch, want_sumsq);
+    if (scatter_only) peer_allreduce_mc_kernel<B2_BF16, true><<<grid, 512, 0, stream>>>(pp, mc, world, rank, v0, v1, scale, epoch, want_sumsq, sumsq_out);
+    else peer_allreduce_mc_kernel<B2_BF16, false><<<grid, 512, 0, stream>>>(pp, mc, world, rank, v0, v1, scale, epoch, want_sumsq, sumsq_out);
   } else {
-    if (scatter_only) peer_allreduce_mc_kernel<B2_F32, true><<<grid, 512, 0, stream>>>(pp, mc, world, rank, v0, v1, scale, epoch, want_sumsq);
-    else peer_allreduce_mc_kernel<B2_F32, false><<<grid, 512, 0, stream>>>(pp, mc, world, rank, v0, v1, scale, epoch, want_sumsq);
+    if (scatter_only) peer_allreduce_mc_kernel<B2_F32, true><<<grid, 512, 0, stream>>>(pp, mc, world, rank, v0, v1, scale, epoch, want_sumsq, sumsq_out);
+    else peer_allreduce_mc_kernel<B2_F32, false><<<grid, 512, 0, stream>>>(pp, mc, world, rank, v0, v1, scale, epoch, want_sumsq, sumsq_out);
   }
   B2_CHECK_CUDA(cudaGetLastError());
   return B2_OK;

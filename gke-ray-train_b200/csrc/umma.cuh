@@ -113,6 +113,13 @@ __device__ __forceinline__ void tma_store_2d_hint(const CUtensorMap* m, const vo
                :: "l"(reinterpret_cast<uint64_t>(m)), "r"(smem_u32(smem_src)), "r"(c0), "r"(c1), "l"(policy) : "memory");
 }
 
+// 32 bytes (one whole sector) from registers to global memory with an L2 eviction hint
+__device__ __forceinline__ void st_global_v8_hint(void* p, uint32_t a, uint32_t b, uint32_t c, uint32_t d, uint32_t e,
+                                                  uint32_t f, uint32_t g, uint32_t h, uint64_t policy) {
+  asm volatile("st.global.L2::cache_hint.v8.b32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8}, %9;"
+               :: "l"(p), "r"(a), "r"(b), "r"(c), "r"(d), "r"(e), "r"(f), "r"(g), "r"(h), "l"(policy) : "memory");
+}
+
 // 2-D tiled store smem -> global (bulk async group); out-of-bounds parts of the box are clipped by the tensor map.
 __device__ __forceinline__ void tma_store_2d(const CUtensorMap* m, const void* smem_src, int c0, int c1) {
   asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%2, %3}], [%1];"

@@ -194,9 +194,15 @@ int b2_gather_windows(const long long* tokens, long long n_tokens, const long lo
  *   everywhere. want_sumsq != 0 additionally leaves, in each rank's flag block, float slot 32 + k = sum of squares
  *   of the reduced values of rank k's slice (k = 0..world-1) — feed those `world` floats to b2_clip_coef.
  *   want_sumsq = 2 keeps adding to the slots instead of restarting them (several bucket calls of one backward pass).
+ *   The per-block partials are added in block order by the last block to finish, so the sums are reproducible run to run.
+ *   sumsq_out (may be NULL): local device array of `world` floats that receives a copy of the `world` slots once they
+ *   are all complete (the kernel's last action) — no separate launch to collect them.
  *   scatter_only != 0 stores the reduced slice of rank r on rank r only (reduce-scatter; see b2_peer_slice).
  *   max_blocks > 0 caps the grid (a bucket reduced while backward kernels still run should not occupy every SM).
- * b2_peer_allgather: pushes this rank's slice of the buffer to every peer (used for updated parameters).
+ * b2_peer_allgather: pushes this rank's slice of elements [offset_elems, offset_elems + n) to every peer (used for
+ *   updated parameters; max_blocks as above).
+ * Slices: rank r's slice of an n-element range is contiguous, the same on every rank, and starts on a 64-element
+ *   boundary relative to the range (b2_peer_slice returns it) — the granularity of b2_adamw_grouped's chunk table.
  * `epoch` must increase by one on every collective call, identically on all ranks (start at 1).
  * Every rank must enqueue the same sequence of calls; the kernels wait for one another inside the GPU, so each
  * rank needs its own device. A peer that never arrives makes the kernel trap after ~10 min instead of hanging. */
@@ -207,16 +213,16 @@ int b2_symm_close(void* dptr);
 int b2_symm_free(void* dptr);
 int b2_peer_allreduce(void* const* peer_bufs, uint32_t* const* peer_flags, int world, int rank, size_t offset_elems,
                       size_t n, int dtype, float scale, unsigned epoch, int want_sumsq, int scatter_only,
-                      int max_blocks, b2_stream_t stream);
+                      int max_blocks, float* sumsq_out, b2_stream_t stream);
 /* NVLS variant of b2_peer_allreduce: `mc_buf` is a multicast address aliasing the same offset of every rank's buffer
  * (cuMulticast* / torch.distributed._symmetric_memory); the sum over ranks is formed inside the NVSwitch
  * (multimem.ld_reduce, fp32 accumulation) and the result is broadcast with multimem.st. Same semantics and arguments
  * otherwise; peer_bufs[rank] must still be the local mapping of the buffer. */
 int b2_peer_allreduce_mc(void* mc_buf, void* const* peer_bufs, uint32_t* const* peer_flags, int world, int rank,
                          size_t offset_elems, size_t n, int dtype, float scale, unsigned epoch, int want_sumsq,
-                         int scatter_only, int max_blocks, b2_stream_t stream);
+                         int scatter_only, int max_blocks, float* sumsq_out, b2_stream_t stream);
 int b2_peer_allgather(void* const* peer_bufs, uint32_t* const* peer_flags, int world, int rank, size_t offset_elems,
-                      size_t n, int dtype, unsigned epoch, b2_stream_t stream);
+                      size_t n, int dtype, unsigned epoch, int max_blocks, b2_stream_t stream);
 int b2_peer_slice(size_t n, int dtype, int world, int rank, size_t* begin, size_t* end);
 
 /* ---- measurement aid (tools/peer_probe.py; no counterpart in the reference) -----------------------------------

@@ -87,49 +87,56 @@ def cpu_gpt2_baseline(steps=2, warmup=1, B=1, T=1024, dtype=torch.float32, threa
                 sample=f"GPT-2 124M {str(dtype).split('.')[-1]} on CPU, B={B} x T={T} per step, {steps} steps after {warmup} warm-up")
 
 
-def _gloo_worker(rank, world, port, steps, warmup, threads, q):
+def small_gpt_gloo_loop(config):
+    """train_loop_per_worker of BASELINE configs[0]: the reference's loop (ref: ray-jobs/pytorch_llm_ray.py:121-312, body
+    :272-279) on its small GPT with `use_gpu=False` => gloo, written against the `ray.train` surface exactly as the
+    reference writes it — here that surface is the b200_train.train shim (ray is not installed), whose prepare_model
+    returns torch's own DistributedDataParallel for CPU workers. Stock torch arithmetic throughout."""
     import torch.distributed as dist
-    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
-    torch.set_num_threads(threads)
-    dist.init_process_group("gloo", rank=rank, world_size=world)
+    from b200_train import train
+    torch.set_num_threads(config["threads"])
+    ctx = train.get_context()
+    rank, world = ctx.get_world_rank(), ctx.get_world_size()
     V = 283
     stream = synthetic_char_stream(vocab=V)
     torch.manual_seed(0)
-    model = nn.parallel.DistributedDataParallel(BasicLLMRestated(V, **SMALL_GPT))      # prepare_model, use_gpu=False
-    opt = torch.optim.AdamW(model.parameters(), lr=REF_LOOP["lr"], weight_decay=REF_LOOP["weight_decay"])
-    crit = nn.CrossEntropyLoss()
+    model = train.torch.prepare_model(BasicLLMRestated(V, **SMALL_GPT))          # ref :230
+    assert next(model.parameters()).device.type == "cpu"
+    opt = torch.optim.AdamW(model.parameters(), lr=REF_LOOP["lr"], weight_decay=REF_LOOP["weight_decay"])   # ref :236
+    crit = nn.CrossEntropyLoss()                                                   # ref :237
     B, T = REF_LOOP["batch_size_per_worker"], REF_LOOP["dataset_seq_len"]
     g = torch.Generator().manual_seed(0)
-    perm = torch.randperm(16000, generator=g)[rank::world]            # DistributedSampler(shuffle=True, seed=0)
+    perm = torch.randperm(16000, generator=g)[rank::world]            # DistributedSampler(shuffle=True, seed=0), ref :206-216
     sched = torch.optim.lr_scheduler.LambdaLR(opt, lr_lambda_factory(len(perm) // B))
     times = []
+    steps, warmup = config["steps"], config["warmup"]
     for s in range(warmup + steps):
         x, y = windows(stream, perm[s * B:(s + 1) * B], T)
-        dist.barrier()
+        if world > 1:
+            dist.barrier()
         t0 = time.perf_counter()
         basic_llm_step(model, opt, sched, crit, x, y, V, REF_LOOP["max_norm"])
-        dist.barrier()
+        if world > 1:
+            dist.barrier()
         if s >= warmup:
             times.append(time.perf_counter() - t0)
-    if rank == 0:
-        q.put(sum(times) / len(times))
-    dist.destroy_process_group()
+    train.report({"sec_per_step": sum(times) / len(times), "threads": torch.get_num_threads()})
 
 
 def cpu_gloo_small_gpt_baseline(steps=5, warmup=2, world=2, threads=None):
     """BASELINE configs[0]: the reference loop (BasicLLM small GPT, synthetic wikitext-2-shaped chars, DDP over gloo,
-    num_workers=2, use_gpu=False) timed on host cores. Returns dict(tokens_per_s, ...)."""
-    import socket
-    import torch.multiprocessing as mp
+    num_workers=2, use_gpu=False) timed on host cores, launched through TorchTrainer(ScalingConfig(num_workers=2,
+    use_gpu=False)) of the trainer shim (ref: ray-jobs/pytorch_llm_ray.py:346-350,362-376). Returns dict(tokens_per_s, ...)."""
+    from b200_train.train import ScalingConfig, TorchConfig, TorchTrainer
     threads = threads or max(1, (os.cpu_count() or 2) // world)
-    with socket.socket() as s:
-        s.bind(("127.0.0.1", 0))
-        port = s.getsockname()[1]
-    ctx = mp.get_context("spawn")
-    q = ctx.SimpleQueue()
-    mp.start_processes(_gloo_worker, args=(world, port, steps, warmup, threads, q), nprocs=world, join=True,
-                       start_method="spawn")
-    sec = q.get()
+    res = TorchTrainer(small_gpt_gloo_loop, train_loop_config={"steps": steps, "warmup": warmup, "threads": threads},
+                       scaling_config=ScalingConfig(num_workers=world, use_gpu=False),
+                       torch_config=TorchConfig(backend="gloo")).fit()
+    if res.error is not None or not res.metrics:
+        raise RuntimeError(f"CPU gloo baseline failed: {res.error!r}")
+    sec = res.metrics["sec_per_step"]
     B, T = REF_LOOP["batch_size_per_worker"], REF_LOOP["dataset_seq_len"]
     return dict(tokens_per_s=world * B * T / sec, ms_per_step=1e3 * sec, cores=os.cpu_count(), threads=threads * world,
-                sample=f"BasicLLM small GPT fp32, {world} gloo workers x {threads} threads, B={B} x T={T} per worker")
+                threads_per_worker=threads, workers=world,
+                sample=f"BasicLLM small GPT fp32 (BASELINE configs[0]), TorchTrainer shim, {world} gloo workers x {threads} "
+                       f"threads, B={B} x T={T} per worker, {steps} steps after {warmup} warm-up")

@@ -72,7 +72,7 @@ def main():
         torch.manual_seed(1000 + rank)                       # ranks start different; prepare_model syncs rank 0's weights
         model = TR.make_gpt2(**{**kw, "seed": rank}).train()
         b200.patch_causal_lm(model)
-        model = b200.prepare_model(model, parallel_strategy_kwargs={"shard_optimizer": shard})
+        model = b200.prepare_model(model, parallel_strategy_kwargs=shard if isinstance(shard, dict) else {"shard_optimizer": shard})
         assert hasattr(model, "module")
         opt = b200.AdamW(TR.hf_param_groups(model.module, 1e-3), lr=2e-4)
         for step in range(2):
@@ -92,6 +92,19 @@ def main():
     model, opt, flat, sd = run_ddp(False)
     model_s, opt_s, flat_s, sd_s = run_ddp(True)
     assert torch.equal(flat, flat_s), "sharded optimizer must give bit-identical parameters"
+    # several buckets per buffer (per-bucket reduce-scatter / AdamW / all-gather), with the parameter all-gather running
+    # under the next forward pass
+    os.environ["B2_DDP_BUCKET_MB"] = "0.25"
+    model_o, opt_o, flat_o, sd_o = run_ddp({"shard_optimizer": True, "overlap_param_sync": True})
+    model_r, opt_r, flat_r, sd_r = run_ddp({"bucket_cap_mb": 0.25})
+    del os.environ["B2_DDP_BUCKET_MB"]
+    assert len(model_o._buckets) > 3 and model_o.overlap_param_sync
+    assert torch.equal(flat, flat_o), "bucketed sharded optimizer must give bit-identical parameters"
+    assert torch.equal(flat, flat_r), "bucket boundaries must not change the result"
+    for k in sd["state"]:
+        assert torch.equal(sd["state"][k]["exp_avg"], sd_o["state"][k]["exp_avg"]), k
+        assert torch.equal(sd["state"][k]["exp_avg_sq"], sd_o["state"][k]["exp_avg_sq"]), k
+    model_o.close(); model_r.close()
     assert sd["state"].keys() == sd_s["state"].keys()
     for k in sd["state"]:
         assert float(sd["state"][k]["step"]) == float(sd_s["state"][k]["step"]) == 2.0
@@ -125,6 +138,31 @@ def main():
     got = torch.cat([p.grad.reshape(-1).float() for p in acc_model.module.parameters()])
     assert (got - local).abs().max() <= 2.0 ** -7 * local.abs().max() + 1e-6
     acc_model.close()
+
+    # --- gradients dropped BETWEEN forward and backward (out = model(x); optimizer.zero_grad(); loss.backward()) with a
+    # foreign optimizer: autograd allocates fresh .grad tensors; they must reach the flat buffer before their bucket is
+    # reduced, or ranks would average stale data and diverge silently
+    torch.manual_seed(11)
+    zg_model = b200.prepare_model(b200.patch_causal_lm(TR.make_gpt2(**kw).train()))
+    zg_opt = torch.optim.AdamW(zg_model.parameters(), lr=1e-3)
+    chk2 = b200.patch_causal_lm(TR.make_gpt2(**kw).to(dev).train())
+    for step in range(2):
+        ids, lab = batches[rank]
+        out = zg_model(input_ids=ids, labels=lab)
+        zg_opt.zero_grad(set_to_none=True)
+        zg_model.flat_buffers[0].grad.fill_(5.0)               # whatever the buffer held before must not be averaged in
+        out.loss.backward()
+        if step == 0:
+            chk2(input_ids=ids, labels=lab).loss.backward()
+            local = torch.cat([p.grad.reshape(-1).float() for p in chk2.parameters()])
+            dist.all_reduce(local); local /= world
+            got = torch.cat([p.grad.reshape(-1).float() for p in zg_model.module.parameters()])
+            assert (got - local).abs().max() <= 2.0 ** -7 * local.abs().max() + 1e-6, "stale gradients were reduced"
+        zg_opt.step()
+    flat_zg = torch.cat([p.detach().float().reshape(-1) for p in zg_model.parameters()])
+    f0 = flat_zg.clone(); dist.broadcast(f0, 0)
+    assert torch.equal(flat_zg, f0), "ranks diverged after forward -> zero_grad -> backward"
+    zg_model.close()
 
     # stock single-process equivalent: DDP averages per-rank mean losses -> emulate by averaging gradients
     ref = TR.make_gpt2(**kw).to(dev).train()

@@ -41,7 +41,7 @@ def test_python_binding_covers_the_header(lib):
 def test_version_and_sizes(lib):
     assert lib.lib.b2_version() == 100
     assert lib.lib.b2_sumsq_scratch_bytes() >= 4 * (32 + 148)
-    assert lib.lib.b2_peer_flags_bytes() == 256
+    assert lib.lib.b2_peer_flags_bytes() == 4 * 384      # barrier words, sumsq slots, per-block partials
     assert lib.lib.b2_lmhead_ce_workspace_bytes(8192) == 2 * 64 * 8192 * 8
     assert lib.lib.b2_lmhead_ce_workspace_bytes(1) == 2 * 64 * 128 * 8
     assert lib.lib.b2_gemm_workspace_bytes(100, 770) == 6 * 100 * 772 * 4
@@ -60,8 +60,8 @@ def test_bad_arguments_are_rejected_without_a_gpu(lib):
     assert L.b2_ce_rows_fwd(16, 0, 4, 0, 0, 16, 0, -100, 16, 16, 16, 16, None, None) == -1
     assert L.b2_lmhead_ce_fwd(16, 8, 16, 8, None, 16, 10, 8, 8, 3, -100, 1, 16, 0, 16, 16, 16, 16, None, None) == -1
     assert b"multiple of shift_T" in L.b2_last_error()
-    assert L.b2_peer_allreduce(None, None, 9, 0, 0, 64, 1, 0.5, 1, 0, 0, 0, None) == -1
-    assert L.b2_peer_allreduce(None, None, 2, 2, 0, 64, 1, 0.5, 1, 0, 0, 0, None) == -1
+    assert L.b2_peer_allreduce(None, None, 9, 0, 0, 64, 1, 0.5, 1, 0, 0, 0, None, None) == -1
+    assert L.b2_peer_allreduce(None, None, 2, 2, 0, 64, 1, 0.5, 1, 0, 0, 0, None, None) == -1
     with pytest.raises(lib.B2Error):
         lib.call("b2_scale", None, 8, 0, None, None)
 
@@ -133,9 +133,9 @@ def test_more_entry_points_reject_bad_arguments(lib):
     assert b"null" in L.b2_last_error()
     assert L.b2_gather_windows(16, 0, 16, 2, 4, 16, 16, None, None) == -1                          # no tokens
     assert L.b2_gather_windows(None, 0, None, 0, 4, None, None, None, None) == 0                   # empty batch: nothing to do
-    assert L.b2_peer_allgather(None, None, 2, 0, 0, 12, 1, 1, None) == -1                          # 12 bf16 != k * 16 bytes
+    assert L.b2_peer_allgather(None, None, 2, 0, 0, 12, 1, 1, 0, None) == -1                          # 12 bf16 != k * 16 bytes
     assert b"16 bytes" in L.b2_last_error()
-    assert L.b2_peer_allgather(None, None, 2, 5, 0, 16, 1, 1, None) == -1
+    assert L.b2_peer_allgather(None, None, 2, 5, 0, 16, 1, 1, 0, None) == -1
     assert L.b2_symm_alloc(0, None, None) == -1
     assert L.b2_lmhead_ce_bwd_dlogits(16, 8, 16, 8, None, 16, 0, 4, 8, 10, 0, -100, 1, 16, 16, 16, 12, None) == -1   # ldd % 8
     assert b"ldd" in L.b2_last_error()

@@ -340,7 +340,7 @@ def test_peer_allreduce_single_gpu_emulation(b200):
         rng = torch.Generator(device="cpu").manual_seed(world)
         bufs = [(torch.randn(n, generator=rng) * 0.1).to(dev(), dtype) for _ in range(world)]
         orig = [b.clone() for b in bufs]
-        flags = [torch.zeros(64, dtype=torch.int32, device=dev()) for _ in range(world)]
+        flags = [torch.zeros(_lib.lib.b2_peer_flags_bytes() // 4, dtype=torch.int32, device=dev()) for _ in range(world)]
         epoch = 5
         for f in flags:
             f[:16] = epoch
@@ -348,7 +348,7 @@ def test_peer_allreduce_single_gpu_emulation(b200):
         ft = (ctypes.c_void_p * world)(*[f.data_ptr() for f in flags])
         for r in range(world):
             _lib.call("b2_peer_allreduce", bt, ft, world, r, 0, n, _lib.dtype_code(dtype), 1.0 / world, epoch, 1, 0, 0,
-                      torch.cuda.current_stream().cuda_stream)
+                      None, torch.cuda.current_stream().cuda_stream)
         torch.cuda.synchronize()
         acc = torch.zeros(n, dtype=torch.float32, device=dev())
         for o in orig:
@@ -367,9 +367,9 @@ def test_peer_allreduce_single_gpu_emulation(b200):
         bt2 = (ctypes.c_void_p * world)(*[b.data_ptr() for b in bufs2])
         for r in range(world):
             _lib.call("b2_peer_allreduce", bt2, ft, world, r, 0, n, _lib.dtype_code(dtype), 1.0 / world, epoch, 0, 1, 0,
-                      torch.cuda.current_stream().cuda_stream)
+                      None, torch.cuda.current_stream().cuda_stream)
         for r in range(world):
-            _lib.call("b2_peer_allgather", bt2, ft, world, r, 0, n, _lib.dtype_code(dtype), epoch,
+            _lib.call("b2_peer_allgather", bt2, ft, world, r, 0, n, _lib.dtype_code(dtype), epoch, 0,
                       torch.cuda.current_stream().cuda_stream)
         torch.cuda.synchronize()
         for b in bufs2:
@@ -458,8 +458,8 @@ def test_adamw_skips_parameters_without_gradient_like_torch(b200):
 
 
 def test_foreign_zero_grad_keeps_flat_gradients(b200):
-    """HF Trainer calls model.zero_grad() (gradients -> None) every step; the patched forward re-installs the flat views so
-    the step still matches the stock path and no per-parameter gradient tensors are allocated."""
+    """HF Trainer calls model.zero_grad() (gradients -> None) every step; each gradient then lands in its slice of the flat
+    buffer as backward produces it (flat.FlatBuffer._land), so the step still matches the stock path."""
     ref_model = _tiny_gpt2().train()
     my_model = b200.patch_causal_lm(copy.deepcopy(ref_model)).train()
     before = {n: p.detach().clone() for n, p in ref_model.named_parameters()}
@@ -477,6 +477,36 @@ def test_foreign_zero_grad_keeps_flat_gradients(b200):
         b200.clip_grad_norm_(my_model.parameters(), 0.3); my_opt.step()
     for (n, a), (_, b) in zip(my_model.named_parameters(), ref_model.named_parameters()):
         _bf16_close(a, b, before[n], n, steps=2)
+
+
+def test_head_gradient_is_written_into_the_flat_buffer(b200):
+    """The LM head's dW goes straight into the parameter's slice of the flat gradient buffer: accumulated there for a tied
+    head (GPT-2: the embedding's share is added in place afterwards), adopted without a copy for an untied one (Llama-3-8B
+    shape). Values against the stock path; two micro-batches exercise the accumulate branch."""
+    from b200_train.flat import flat_of
+    tied = _tiny_gpt2().train()
+    untied = TR.make_llama(dtype=torch.bfloat16, seed=0, vocab_size=4099, hidden_size=128, intermediate_size=256,
+                           num_hidden_layers=2, num_attention_heads=4, num_key_value_heads=2, head_dim=32,
+                           tie_word_embeddings=False, max_position_embeddings=128).to(dev()).train()
+    for ref_model, vocab in ((tied, 2003), (untied, 4099)):
+        my_model = b200.patch_causal_lm(copy.deepcopy(ref_model)).train()
+        my_opt = b200.AdamW(TR.hf_param_groups(my_model, 1e-3), lr=2e-4)
+        head = my_model.get_output_embeddings().weight
+        buf, _ = flat_of(head)
+        view = buf.grad_view(buf._index[id(head)])
+        batches = [TR.synthetic_hf_batch(2, 64, vocab, seed=300 + i, device=dev()) for i in range(2)]
+        n_items = sum(int((lab[:, 1:] != -100).sum()) for _, lab in batches)
+        my_opt.zero_grad(set_to_none=True)
+        buf.grad.fill_(3.0)                                      # stale contents must not survive
+        for k, (ids, lab) in enumerate(batches):
+            ref_model(input_ids=ids, labels=lab, num_items_in_batch=n_items).loss.backward()
+            my_model(input_ids=ids, labels=lab, num_items_in_batch=n_items).loss.backward()
+            assert head.grad is view, f"micro-batch {k}: .grad is not the flat slice"
+        got, want = head.grad.float(), ref_model.get_output_embeddings().weight.grad.float()
+        rel = float((got - want).norm() / want.norm())
+        assert rel < 1e-2, rel
+        for (n, a), (_, b) in zip(my_model.named_parameters(), ref_model.named_parameters()):
+            assert float((a.grad.float() - b.grad.float()).norm()) <= 2e-2 * float(b.grad.float().norm()) + 1e-6, n
 
 
 def test_out_of_range_label_raises_when_asked(b200):

@@ -20,18 +20,33 @@ def test_flatten_keeps_parameters_and_values():
     assert [id(p) for p in m.parameters()] == ids                       # same Parameter objects
     for n, p in m.named_parameters():
         assert torch.equal(p, before[n])
-        assert p.grad is not None and p.grad.shape == p.shape and float(p.grad.abs().sum()) == 0.0
+        assert p.grad is None                                            # as in torch: no gradient before a backward
         assert p._b2_flat[1] % ALIGN == 0
-    # autograd accumulates into the flat gradient buffer in place
-    m(torch.randn(4, 5)).sum().backward()
+    # the first backward's gradients LAND in the flat gradient buffer (copied in by the buffer's hook, not added to a
+    # zero-filled buffer) ...
+    x = torch.randn(4, 5)
+    ref = [g.clone() for g in torch.autograd.grad(m(x).sum(), list(m.parameters()))]
     buf = bufs[0]
-    assert float(buf.grad.abs().sum()) > 0
+    buf.grad.fill_(7.0)                                                 # stale contents must not leak into the result
+    m(x).sum().backward()
     for i, p in enumerate(buf.params):
         assert p.grad.data_ptr() == buf.grad_view(i).data_ptr()
-    # a dropped .grad is re-installed; a foreign .grad is adopted by copy
-    p0 = buf.params[0]
+        assert torch.equal(p.grad, ref[i])
+    # ... and a second backward accumulates in place, like any torch gradient
+    m(x).sum().backward()
+    for i, p in enumerate(buf.params):
+        assert p.grad is buf.grad_view(i) and torch.allclose(p.grad, 2 * ref[i])
+    # zero_grad(set_to_none=True) drops them (nothing is zero-filled) and the next backward lands again
+    buf.zero_grad()
+    assert all(p.grad is None for p in buf.params)
+    m(x).sum().backward()
+    assert all(torch.equal(p.grad, r) for p, r in zip(buf.params, ref))
+    # a foreign .grad is adopted by copy; a parameter without a gradient contributes a zeroed slice
+    p0, p1 = buf.params[0], buf.params[1]
     p0.grad = torch.ones_like(p0)
+    p1.grad = None
     assert buf.install_grads() == 1 and torch.equal(buf.grad_view(0), torch.ones_like(p0))
+    assert p1.grad is buf.grad_view(1) and float(p1.grad.abs().sum()) == 0.0
     again = flatten_params(list(m.parameters()))
     assert again == bufs                                                # idempotent
     assert buffers_of(list(m.parameters()))[0] == bufs
@@ -150,6 +165,40 @@ def test_trainer_shim_two_gloo_workers(tmp_path):
     assert result.error is None
     assert np.isfinite(result.metrics["loss"]) and "checksum" in result.metrics
     assert result.checkpoint is not None and os.path.exists(os.path.join(result.checkpoint.path, "model.pth"))
+
+
+def _dying_loop(config):
+    import os as _os
+    from b200_train import train
+    if train.get_context().get_world_rank() == 1:
+        _os._exit(3)                      # dies without reporting anything (OOM kill, segfault in native code, ...)
+    import time as _time
+    _time.sleep(600)                      # the survivor would wait in a collective forever
+
+
+def test_trainer_shim_surfaces_a_worker_that_dies_without_reporting():
+    """fit() must neither hang on the queue nor return while workers still run."""
+    import time
+    from b200_train.train import ScalingConfig, TorchConfig, TorchTrainer
+    t0 = time.time()
+    res = TorchTrainer(_dying_loop, train_loop_config={}, scaling_config=ScalingConfig(num_workers=2, use_gpu=False),
+                       torch_config=TorchConfig(backend="gloo")).fit()
+    assert res.error is not None and res.metrics is None
+    assert time.time() - t0 < 120
+
+
+def test_front_parameters_get_their_own_bucket():
+    """Embeddings sit at the front of the flat buffer and receive their gradient last: they must not hold back the
+    bucket of the first transformer layers."""
+    from b200_train.ddp import plan_buckets
+    offsets = [0, 1000, 1100, 1200, 1300, 1400]
+    plan = plan_buckets(offsets, 1500, 2, cap_bytes=400, front_params=2)
+    assert plan[-1] == (0, 1100, [1, 0])                                  # the two leading parameters, launched last
+    assert sum(n for _, n, _ in plan) == 1500 and plan[0][0] + plan[0][1] == 1500
+    assert sorted(i for _, _, m in plan for i in m) == list(range(6))
+    for (s0, n0, _), (s1, n1, _) in zip(plan, plan[1:]):
+        assert s1 + n1 == s0                                              # contiguous, back to front
+    assert plan_buckets(offsets, 1500, 2, cap_bytes=1 << 40, front_params=0) == [(0, 1500, [5, 4, 3, 2, 1, 0])]
 
 
 def test_trainer_shim_single_worker_inline():

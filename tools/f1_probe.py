@@ -44,7 +44,7 @@ def main():
     W = (torch.randn(V, D, generator=g) * 0.05).to(dev, torch.bfloat16)
     y = torch.randint(0, V, (N,), generator=g).to(dev)
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
-    ldd = (V + 7) // 8 * 8
+    ldd = (V + 63) // 64 * 64          # row pitch: a multiple of 128 bytes
     chunk = min(args.chunk, N)
     dl = torch.empty(chunk, ldd, dtype=torch.bfloat16, device=dev)
     dH = torch.empty(N, D, dtype=torch.bfloat16, device=dev)
