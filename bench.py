@@ -28,6 +28,7 @@ sys.path.insert(0, os.path.join(ROOT, "gke-ray-train_b200"))
 
 B_PER_GPU, SEQ, MAX_NORM, LR, WD = 8, 1024, 0.3, 2e-4, 1e-3
 METRIC = "train tokens/sec/box"
+F1_TRAFFIC_KEPT, F1_TRAFFIC_RECOMPUTE = 4.76e9, 3.24e9      # measured DRAM bytes per step of the F1 family (see f1_roofline)
 # --workload: the default is the configuration BASELINE.json's metric is quoted on at N=1 (configs[1]); llama-1b is
 # configs[2] (Llama-3.2-1B shape, seq 2048, 2 sequences x 4 accumulation steps per GPU, ref: fine_tune_config.json:13-14)
 WORKLOADS = {
@@ -105,6 +106,7 @@ def run_reference(args):
     steps = max(1, min(args.steps, 3))
     warm = max(1, min(args.warmup, 1))
     r = TR.cpu_gpt2_baseline(steps=steps, warmup=warm, B=1, T=SEQ, dtype=torch.bfloat16)
+    gloo = configs0_gloo_baseline(TR)
     line = {
         "impl": "reference", "metric": METRIC, "value": r["tokens_per_s"], "unit": "tokens/s", "n_gpus": args.gpus,
         "steps": steps, "warmup": warm, "ms_per_step": r["ms_per_step"], "higher_is_better": True, "scaling": "weak",
@@ -112,11 +114,39 @@ def run_reference(args):
         "config": {"workload": "gpt2-124m full fine-tune, seq 1024, bf16 (BASELINE configs[1])",
                    "note": "reference = stock torch/transformers step (HF loss, clip_grad_norm_, torch.optim.AdamW) on host cores; "
                            "bounded sample; ray/trl/accelerate are not installed so the loop body is restated in oracle/torch_ref.py"},
-        "cpu_baseline": {"value": r["tokens_per_s"], "unit": "tokens/s", "cores": r["threads"], "kind": "port", "sample": r["sample"]},
+        "cpu_baseline": {"value": r["tokens_per_s"], "unit": "tokens/s", "cores": r["threads"], "kind": "port", "sample": r["sample"],
+                         "configs0_gloo": gloo},
         "e2e": {"value": r["tokens_per_s"], "unit": "tokens/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
     print(json.dumps(line), flush=True)
+
+
+def configs0_gloo_baseline(TR):
+    """BASELINE configs[0], the reference's own CPU-runnable case (ref: ray-jobs/pytorch_llm_ray.py:346-350,362-376):
+    small GPT, TorchTrainer(ScalingConfig(num_workers=2, use_gpu=False)) => gloo, through the trainer shim, at the two
+    thread settings SURVEY.md §8(d) names: Ray-faithful 1 thread per worker, and cores/2 per worker. A different model
+    than the headline workload, so it is reported NEXT TO the GPT-2 sample, not as `value`."""
+    out = {"host_cores": os.cpu_count(), "workers": 2, "backend": "gloo", "launcher": "b200_train.train.TorchTrainer (ray is not installed)"}
+    # under torchrun this process carries RANK / WORLD_SIZE of the GPU job: the trainer must start its own two workers
+    saved = {k: os.environ.pop(k) for k in ("RANK", "LOCAL_RANK", "WORLD_SIZE", "MASTER_ADDR", "MASTER_PORT",
+                                            "LOCAL_WORLD_SIZE", "GROUP_RANK", "ROLE_RANK", "TORCHELASTIC_RUN_ID")
+             if k in os.environ}
+    try:
+        _configs0_runs(TR, out)
+    finally:
+        os.environ.update(saved)
+    return out
+
+
+def _configs0_runs(TR, out):
+    for name, threads in (("threads_1_per_worker", 1), ("threads_half_cores_per_worker", max(1, (os.cpu_count() or 2) // 2))):
+        try:
+            g = TR.cpu_gloo_small_gpt_baseline(steps=3, warmup=1, world=2, threads=threads)
+            out[name] = {"value": g["tokens_per_s"], "unit": "tokens/s", "ms_per_step": g["ms_per_step"],
+                         "threads_per_worker": threads, "sample": g["sample"]}
+        except Exception as e:  # noqa: BLE001 - a baseline that cannot run is reported, it does not sink the bench line
+            out[name] = {"error": repr(e)[:300]}
 
 
 # ------------------------------------------------------------------------------------------------ our arm
@@ -194,8 +224,11 @@ def f1_roofline(torch, b200, model, device, peaks, iters=5):
             "frac": achieved / peaks["bf16_tflops"],
             # dram read+write summed over the family's launches from ncu --set full (profiles/README.md): measured for the
             # recompute route only (3.13e9); the kept-logits route has not been captured yet
-            "traffic": None if keep else 3.13e9,
-            "traffic_recompute_route": 3.13e9,
+            # dram__bytes_read + dram__bytes_write summed over the family's launches, one `ncu --set full` capture per route
+            # (profiles/r2_f1_ncu_metrics.json): kept route 0.89 (forward+store) + 1.59 (in-place gradient) + 1.17 (dH incl.
+            # split-K reduce) + 1.12 (dW) GB; recompute route 0.09 + 0.86 + 1.17 + 1.12 GB. Algorithmic (no N*V term): 0.347 GB
+            "traffic": F1_TRAFFIC_KEPT if keep else F1_TRAFFIC_RECOMPUTE,
+            "traffic_recompute_route": F1_TRAFFIC_RECOMPUTE,
             "route": "kept-logits" if keep else "recompute",
             "kernel": kernel,
             "ms": ms, "algorithmic_flops": flops, "launches": parts, "dlogits_recompute_route": other,
@@ -223,6 +256,113 @@ def f3_roofline(torch, ops, device, peaks, n=1 << 27, iters=5):
     gbs = 14.0 * n / (ms * 1e-3) / 1e9
     return {"bound": "hbm", "achieved": gbs, "peak": peaks["hbm_gbs"], "unit": "GB/s", "frac": gbs / peaks["hbm_gbs"],
             "traffic": 1.823e9, "kernel": "adamw_kernel (pure bf16, n=2^27; 14 B/element = 1.879e9 algorithmic bytes)", "ms": ms}
+
+
+def f2_parity_check(torch, dist, model, optimizer, ops, batch, B):
+    """N > 1, before anything is timed: is what the peer-memory kernels leave in the flat gradient buffer the mean over
+    ranks? One un-timed backward under no_sync() gives this rank's LOCAL gradients; NCCL — as the checker only — forms
+    their mean in fp32; then the wrapper's own bucketed reduction (model.reduce_gradients(): same kernels, same buckets
+    as the timed steps) runs and is compared: max error in bf16 ulps, identical bits on every rank, and the fused sum
+    of squares against b2_sumsq of the reduced buffer. With a sharded optimizer only this rank's slices are compared."""
+    rank, world = dist.get_rank(), dist.get_world_size()
+    ids, lab = batch
+    optimizer.zero_grad(set_to_none=True)
+    with model.no_sync():
+        model(input_ids=ids[:B], labels=lab[:B]).loss.backward()
+    res = {"f2": "ok", "max_ulp": 0.0, "kernel": None, "identical_across_ranks": True, "sumsq_rel_err": 0.0,
+           "sharded": bool(model.shard_optimizer), "buckets": len(model._buckets)}
+    refs = []
+    for buf in model.flat_buffers:
+        buf.install_grads()
+        ref = buf.grad.float()
+        dist.all_reduce(ref)                               # NCCL: the checker
+        refs.append((ref * (1.0 / world)).to(buf.dtype))
+    model.reduce_gradients()
+    torch.cuda.synchronize()
+    for buf, ref in zip(model.flat_buffers, refs):
+        res["kernel"] = model.comm.kernel_name(buf.grad)
+        segs = [(lo, hi) for lo, hi, _ in buf.shards] if buf.shards is not None else [(0, buf.numel)]
+        got = torch.cat([buf.grad[lo:hi] for lo, hi in segs]).float()
+        want = torch.cat([ref[lo:hi] for lo, hi in segs]).float()
+        mant_bits = 8 if buf.dtype == torch.bfloat16 else 24
+        ulp = torch.ldexp(torch.ones_like(want), torch.frexp(want.abs().clamp_min(1e-30))[1] - mant_bits)
+        res["max_ulp"] = max(res["max_ulp"], float(((got - want).abs() / ulp).max()))
+        if buf.shards is None:                             # replicated result: every rank must hold the same bits
+            chk = buf.grad.view(torch.int16 if buf.dtype == torch.bfloat16 else torch.int32).to(torch.int64).sum().reshape(1)
+            all_chk = [torch.empty_like(chk) for _ in range(world)]
+            dist.all_gather(all_chk, chk)
+            res["identical_across_ranks"] &= all(int(c) == int(all_chk[0]) for c in all_chk)
+            fused, direct = float(buf.reduced_sumsq.double().sum()), float(ops.sumsq(buf.grad).item())
+        else:
+            fused, direct = float(buf.reduced_sumsq[rank]), float(sum(ops.sumsq(buf.grad[lo:hi]).item() for lo, hi in segs if hi > lo))
+        res["sumsq_rel_err"] = max(res["sumsq_rel_err"], abs(fused - direct) / max(direct, 1e-30))
+    # W = 2: the fp32 sum of two values is exact, so the kernels must agree with NCCL bit for bit; W > 2: summation order
+    # (ours: rank order; NVLS: inside the switch; NCCL: ring) may differ by one rounding of the result
+    tol = 0.0 if world == 2 else (1.0 if all(b.dtype == torch.bfloat16 for b in model.flat_buffers) else 4.0)
+    ok = res["max_ulp"] <= tol and res["identical_across_ranks"] and res["sumsq_rel_err"] < 1e-4
+    flag = torch.tensor([0 if ok else 1], device=ids.device)
+    dist.all_reduce(flag)
+    if int(flag):
+        res["f2"] = "mismatch"
+    optimizer.zero_grad(set_to_none=True)
+    return res
+
+
+def f2_roofline(torch, dist, comm, device, n, label, iters=8):
+    """The peer-memory all-reduce alone on an n-element bf16 symmetric buffer: CUDA events on the launching stream, max
+    over ranks, NCCL's all_reduce timed the same way beside it. Algorithmic bytes per GPU per direction = 2 (W-1)/W n s
+    (the busbw convention; with the in-switch NVLS reduction each GPU actually moves about n s, so > 100 % of the link
+    figure is possible and is labelled by `kernel`)."""
+    world = dist.get_world_size()
+    t = comm.alloc(n, torch.bfloat16, device)
+    t.normal_(0, 1e-2)
+    ref = torch.empty(n, dtype=torch.bfloat16, device=device).normal_(0, 1e-2)
+
+    def timed(fn):
+        ts = []
+        for it in range(iters + 2):
+            dist.barrier()
+            torch.cuda.synchronize()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record(); fn(); e1.record()
+            torch.cuda.synchronize()
+            if it >= 2:
+                ts.append(e0.elapsed_time(e1))
+        ms = torch.tensor([sum(ts) / len(ts)], device=device)
+        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        return float(ms.item())
+
+    ms = timed(lambda: comm.allreduce_(t, want_sumsq=True))
+    ms_nccl = timed(lambda: dist.all_reduce(ref))
+    bytes_dir = 2.0 * (world - 1) / world * n * 2
+    gbs = bytes_dir / (ms * 1e-3) / 1e9
+    return {"bound": "nvlink", "achieved": gbs, "peak": 900.0, "unit": "GB/s", "frac": gbs / 900.0,
+            "peak_source": "NVLink 5 nominal, per direction per GPU (a plain peer copy from a kernel sustains ~775 here: profiles/r1_nvlink_raw_copy_probe.txt)",
+            "traffic": None, "ms": ms, "algorithmic_bytes": bytes_dir, "world": world,
+            "kernel": f"peer_allreduce ({comm.kernel_name(t)}) + fused 1/W scale + sum of squares, {label}",
+            "nccl_ms": ms_nccl, "nccl_busbw_gbs": bytes_dir / (ms_nccl * 1e-3) / 1e9}
+
+
+def stock_gpu_steps(torch, TR, device, vocab=None, steps=3, warmup=2):
+    """Informational: the reference's stock torch path (HF loss, clip_grad_norm_, torch.optim.AdamW) on THIS GPU, same
+    model / batch shape, a few steps. vocab=50304 pads the vocabulary to a multiple of 64 — cuBLAS runs the V = 50257
+    head at ~100 TFLOP/s, which flatters any comparison with it."""
+    kw = {} if vocab is None else {"vocab_size": vocab}
+    model = TR.make_gpt2(dtype=torch.bfloat16, seed=0, **kw).to(device).train()
+    opt = torch.optim.AdamW(TR.hf_param_groups(model, WD), lr=LR)
+    ids, lab = TR.synthetic_hf_batch(B_PER_GPU, SEQ, 50257, 1234, device=device)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    for s in range(warmup + steps):
+        if s == warmup:
+            torch.cuda.synchronize()
+            e0.record()
+        opt.zero_grad(set_to_none=True)
+        model(input_ids=ids, labels=lab).loss.backward()
+        torch.nn.utils.clip_grad_norm_(model.parameters(), MAX_NORM)
+        opt.step()
+    e1.record()
+    torch.cuda.synchronize()
+    return e0.elapsed_time(e1) / steps
 
 
 def run_ours(args):
@@ -262,7 +402,11 @@ def run_ours(args):
         clip = torch.nn.utils.clip_grad_norm_
     else:
         b200.patch_causal_lm(model)
-        model = b200.prepare_model(model)                   # .to(device); peer-memory DDP when world > 1
+        # .to(device); peer-memory DDP when world > 1 (--shard-optimizer: reduce-scatter -> AdamW on the shard -> all-gather)
+        psk = None
+        if args.shard_optimizer:
+            psk = {"shard_optimizer": True, "overlap_param_sync": args.shard_optimizer >= 2}
+        model = b200.prepare_model(model, parallel_strategy_kwargs=psk)
         inner = model.module if hasattr(model, "module") else model
         optimizer = b200.AdamW(TR.hf_param_groups(inner, WD), lr=LR)
         clip = b200.clip_grad_norm_
@@ -323,6 +467,16 @@ def run_ours(args):
     for s in range(max(args.warmup, 3)):
         step(*resident[s % n_batches])
     torch.cuda.synchronize()
+    parity = None
+    if world > 1 and not stock:
+        parity = f2_parity_check(torch, dist, model, optimizer, ops, resident[0], B_PER_GPU)
+        if parity["f2"] != "ok":
+            if rank == 0:
+                print(json.dumps({"error": "peer-memory gradient reduction disagrees with the NCCL check", "parity_check": parity}), flush=True)
+            raise SystemExit(3)
+        step(*resident[0])                                  # back to a normal step before timing
+        torch.cuda.synchronize()
+    mem_gb = torch.cuda.max_memory_allocated(device) / 1e9
 
     sampler = ClockSampler(local_rank) if rank == 0 else None
     if sampler:
@@ -336,17 +490,32 @@ def run_ours(args):
     e2e = tokens_per_step * args.steps / (ms_e2e * 1e-3)
 
     roof = cpu = extra = None
+    f2 = []
+    if world > 1 and not stock:
+        # F2 alone (all ranks take part): on a buffer the size of this model's flat gradients, and on configs[4]'s 2^30 bf16
+        n_model = sum(b.numel for b in model.flat_buffers)
+        f2.append(f2_roofline(torch, dist, model.comm, device, n_model, f"n = {n_model} bf16 (this model's flat gradient buffer)"))
+        if not args.no_f2_large:
+            f2.append(f2_roofline(torch, dist, model.comm, device, 1 << 30, "n = 2^30 bf16 (BASELINE configs[4])"))
     if rank == 0 and not stock:
         roof = f1_roofline(torch, b200, inner, device, peaks)
-        extra = [f3_roofline(torch, ops, device, peaks)]
+        extra = [f3_roofline(torch, ops, device, peaks)] + f2
     if world > 1:
         dist.barrier()
+    stock_ms = None
+    if rank == 0 and world == 1 and not stock and args.workload == "gpt2-124m" and not args.no_stock:
+        del optimizer
+        stock_ms = {"stock_gpu_ms_per_step": stock_gpu_steps(torch, TR, device),
+                    "stock_gpu_ms_per_step_vocab_padded_to_50304": stock_gpu_steps(torch, TR, device, vocab=50304),
+                    "note": "the reference's stock torch path on this GPU, 3 steps after 2 warm-up (informational; "
+                            "the padded-vocabulary run takes cuBLAS's misaligned-N slowdown out of the comparison)"}
     if rank == 0 and world == 1 and not args.no_cpu_baseline and not stock and args.workload == "gpt2-124m":
         # the one place this arm touches oracle/: the reported CPU baseline (the reference's stock call sequence)
         from oracle import torch_ref as REF
         torch.set_num_threads(os.cpu_count() or 1)
         r = REF.cpu_gpt2_baseline(steps=2, warmup=1, B=1, T=SEQ, dtype=torch.bfloat16)
-        cpu = {"value": r["tokens_per_s"], "unit": "tokens/s", "cores": r["threads"], "kind": "port", "sample": r["sample"]}
+        cpu = {"value": r["tokens_per_s"], "unit": "tokens/s", "cores": r["threads"], "kind": "port", "sample": r["sample"],
+               "configs0_gloo": configs0_gloo_baseline(REF)}
     if rank == 0:
         line = {
             **({"impl": "stock-gpu"} if stock else {}),
@@ -355,13 +524,16 @@ def run_ours(args):
             "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
             "config": {"workload": wl["desc"], "global_batch": world * B_PER_GPU * GA, "grad_accum": GA,
                        "seq_len": SEQ, "parallelism": f"dp{world}",
-                       "optimizer": "AdamW lr 2e-4 wd 1e-3, clip 0.3, pure-bf16 state",
+                       "optimizer": "AdamW lr 2e-4 wd 1e-3, clip 0.3, pure-bf16 state"
+                                    + (", sharded over ranks (reduce-scatter / AdamW on the shard / all-gather"
+                                       + (", gather under the next forward)" if args.shard_optimizer >= 2 else ")") if args.shard_optimizer and world > 1 else ""),
                        "l2": "no explicit flush between steps: one step streams params+grads+AdamW state (1.0 GB) and >4 GB of "
                              "activations, far beyond the 126 MB L2; the roofline micro-runs flush 256 MB between iterations",
                        "last_loss": last_loss},
             "e2e": {"value": e2e, "unit": "tokens/s", "h2d_bytes_per_step": 2 * B_PER_GPU * GA * SEQ * 8, "d2h_bytes_per_step": 4,
                     "ms_per_step": ms_e2e / args.steps},
             "gpu_launches": launches, "clocks": clocks, "roofline": roof, "rooflines_other": extra, "cpu_baseline": cpu,
+            "parity_check": parity, "stock_gpu": stock_ms, "max_memory_allocated_gb": mem_gb,
         }
         print(json.dumps(line), flush=True)
     if world > 1:
@@ -378,6 +550,10 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference", "stock-gpu"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-stock", action="store_true", help="skip the informational stock-torch-on-this-GPU steps")
+    ap.add_argument("--no-f2-large", action="store_true", help="N > 1: skip the 2^30-element all-reduce microbenchmark")
+    ap.add_argument("--shard-optimizer", type=int, default=0, choices=[0, 1, 2],
+                    help="N > 1: 1 = reduce-scatter / AdamW on the shard / all-gather; 2 = also overlap the all-gather with the next forward")
     ap.add_argument("--workload", default="gpt2-124m", choices=sorted(WORKLOADS))
     args = ap.parse_args()
     if args.impl == "reference":
@@ -387,7 +563,8 @@ def main():
         # convenience: re-launch ourselves one rank per GPU
         cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={args.gpus}",
                "--master-addr", "127.0.0.1", "--master-port", "29517", os.path.abspath(__file__), "--gpus", str(args.gpus),
-               "--steps", str(args.steps), "--warmup", str(args.warmup), "--impl", args.impl, "--workload", args.workload] + (["--no-cpu-baseline"] if args.no_cpu_baseline else [])
+               "--steps", str(args.steps), "--warmup", str(args.warmup), "--impl", args.impl, "--workload", args.workload, "--shard-optimizer", str(args.shard_optimizer)]
+        cmd += (["--no-cpu-baseline"] if args.no_cpu_baseline else []) + (["--no-f2-large"] if args.no_f2_large else [])
         raise SystemExit(subprocess.call(cmd))
     run_ours(args)
 

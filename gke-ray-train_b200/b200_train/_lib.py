@@ -77,10 +77,13 @@ _SIGS = {
     "b2_peer_allgather": (c_int, [c_void_p, c_void_p, c_int, c_int, c_size_t, c_size_t, c_int, ctypes.c_uint, c_int,
                                   c_void_p]),
     "b2_peer_slice": (c_int, [c_size_t, c_int, c_int, c_int, c_void_p, c_void_p]),
+}
+# measurement aids: exported only by a library built with B2_BUILD_PROBES=1 (load it with B2_LIB=...)
+_PROBE_SIGS = {
     "b2_debug_peer_copy": (c_int, [c_void_p, c_void_p, c_size_t, c_int, c_int, c_int, c_void_p]),
 }
 
-for _name, (_res, _args) in _SIGS.items():
+for _name, (_res, _args) in list(_SIGS.items()) + [kv for kv in _PROBE_SIGS.items() if hasattr(lib, kv[0])]:
     _fn = getattr(lib, _name)
     _fn.restype = _res
     _fn.argtypes = _args

@@ -7,6 +7,12 @@ One sum-of-squares launch per flat gradient buffer, one scalar kernel for the co
 parameters belong to a b200_train.AdamW — NO pass to scale the gradients: the coefficient stays on the device and
 the optimizer kernel multiplies by it as it reads each gradient. Otherwise the gradients are scaled in place.
 Returns the total norm as a 0-dim device tensor, like torch (no host sync).
+
+Deviation from torch, and how to switch it off: with a b200_train.AdamW attached, `.grad` still holds the UNCLIPPED
+values after this call (torch scales them in place, $SP/torch/nn/utils/clip_grad.py:165-183); only the optimizer step sees
+the clipped ones. Code that reads or logs gradients between clip and step should pass `defer_to_optimizer=False` (one
+extra read+write pass over the gradients, exactly torch's behaviour). A second deferred call before step() composes with
+the first one the way two in-place clips would: it is given the norm of the already-clipped gradients.
 """
 import torch
 
@@ -16,7 +22,8 @@ from .flat import buffers_of, flat_of
 
 
 @torch.no_grad()
-def clip_grad_norm_(parameters, max_norm, norm_type=2.0, error_if_nonfinite=False, foreach=None):
+def clip_grad_norm_(parameters, max_norm, norm_type=2.0, error_if_nonfinite=False, foreach=None, *,
+                    defer_to_optimizer=True):
     if isinstance(parameters, torch.Tensor):
         parameters = [parameters]
     params = [p for p in parameters if p.grad is not None]
@@ -62,16 +69,27 @@ def clip_grad_norm_(parameters, max_norm, norm_type=2.0, error_if_nonfinite=Fals
             first = False
         pieces.append(part)
     parts = pieces[0] if len(pieces) == 1 else torch.cat(pieces)
+    # an earlier clip whose coefficient is still waiting for the optimizer: these gradients count as already scaled by it
+    earlier = None
+    for buf in bufs:
+        if buf.pending_coef is not None:
+            earlier = buf.pending_coef
+            break
+    if earlier is not None:
+        parts = parts * (earlier * earlier)
     norm, coef = ops.clip_coef(parts, max_norm)
+    if earlier is not None:
+        coef = coef * earlier
     if error_if_nonfinite and not bool(torch.isfinite(norm).item()):
         raise RuntimeError(f"The total norm of order {norm_type} for gradients from `parameters` is non-finite, "
                            "so it cannot be clipped.")
     for buf in bufs:
         whole = whole_all or all(id(p) in covered for p in buf.params)
-        if whole and buf.optimizer_attached:
+        if whole and buf.optimizer_attached and defer_to_optimizer:
             buf.pending_coef = coef                             # consumed by the next AdamW.step()
         elif whole:
             ops.scale_(buf.grad, coef)
+            buf.pending_coef = None                             # (an earlier deferred coefficient is part of `coef`)
         else:
             for i, p in enumerate(buf.params):
                 if id(p) in covered:

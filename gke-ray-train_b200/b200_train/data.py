@@ -57,6 +57,16 @@ class ResidentWindowLoader:
         return x, y
 
     def __iter__(self):
-        order = torch.tensor(list(iter(self.sampler)), dtype=torch.int64).to(self.device, non_blocking=True)
+        idx = list(iter(self.sampler))
+        # the kernel flags a window that does not fit the token stream and zero-fills it; the reference's __getitem__
+        # would hand collate a short tensor and fail there. Window starts come from the sampler, so they are checked on
+        # the host, before anything is gathered — no device flag to poll.
+        if idx and (min(idx) < 0 or max(idx) + self.seq_len + 1 > self.tokens.numel()):
+            raise IndexError(f"window start outside [0, {self.tokens.numel() - self.seq_len - 1}] for seq_len {self.seq_len}")
+        order = torch.tensor(idx, dtype=torch.int64).to(self.device, non_blocking=True)
         for i in range(len(self)):
             yield self.gather(order[i * self.batch_size:(i + 1) * self.batch_size])
+
+    def check(self):
+        """True if no gather since construction met an out-of-range window (one host sync; for callers of gather())."""
+        return int(self._err.item()) == 0

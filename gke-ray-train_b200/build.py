@@ -29,6 +29,15 @@ def _newer(src, dst, deps):
 
 
 def build(force=False, verbose=False):
+    """B2_BUILD_PROBES=1 in the environment adds -DB2_BUILD_PROBES: the measurement aids (B2_DEBUG_STORE / B2_DEBUG_NOEPI
+    branches, b2_debug_peer_copy) are compiled in. The default build, the one that ships, has none of them."""
+    global OBJ, OUT
+    flags = list(FLAGS)
+    if os.environ.get("B2_BUILD_PROBES") == "1":
+        flags += ["-DB2_BUILD_PROBES"]
+        OBJ = os.path.join(HERE, "build", "probes")
+        OUT = os.path.join(HERE, "build", "ab", "libb2train_probes.so")
+        os.makedirs(os.path.dirname(OUT), exist_ok=True)
     os.makedirs(OBJ, exist_ok=True)
     srcs = sorted(f for f in os.listdir(CSRC) if f.endswith(".cu"))
     hdrs = [os.path.join(CSRC, f) for f in os.listdir(CSRC) if f.endswith((".cuh", ".h"))]
@@ -41,7 +50,7 @@ def build(force=False, verbose=False):
         obj = os.path.join(OBJ, f[:-3] + ".o")
         objs.append(obj)
         if force or _newer(src, obj, hdrs):
-            cmd = [NVCC] + FLAGS + (["-Xptxas", "-v"] if verbose else []) + ["-c", src, "-o", obj]
+            cmd = [NVCC] + flags + (["-Xptxas", "-v"] if verbose else []) + ["-c", src, "-o", obj]
             jobs.append(cmd)
 
     def run(cmd):

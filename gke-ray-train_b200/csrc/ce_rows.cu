@@ -60,11 +60,13 @@ __global__ void __launch_bounds__(256) ce_rows_fwd_kernel(const void* __restrict
 }
 
 template <int DT>
-__global__ void __launch_bounds__(256) ce_rows_bwd_kernel(const void* __restrict__ logits, long long N, long long V,
+// (logits / dlogits carry no __restrict__: the ABI lets dlogits alias logits — the gradient may overwrite the logits in
+// place — and a restrict-qualified const input could be read through the non-coherent path while being written)
+__global__ void __launch_bounds__(256) ce_rows_bwd_kernel(const void* logits, long long N, long long V,
                                                           long long ld, const long long* __restrict__ labels,
                                                           int shift_T, long long ignore_index,
                                                           const float* __restrict__ lse, const float* __restrict__ gscale,
-                                                          void* __restrict__ dlogits) {
+                                                          void* dlogits) {
   using L = Vec8<DT>;
   const float gs = __ldg(gscale);
   for (long long row = blockIdx.x; row < N; row += gridDim.x) {

@@ -91,6 +91,16 @@ struct Params {
                                      // (no shared-memory staging, no TMA store); needs p.dlogits / p.ldd
 };
 
+// Measurement aids (B2_DEBUG_STORE / B2_DEBUG_NOEPI, tools/f1_probe.py) exist only in a library built with
+// -DB2_BUILD_PROBES (`B2_BUILD_PROBES=1 python build.py`); the shipped kernels carry none of their branches.
+__device__ __forceinline__ bool probe_skips_store(const Params& p) {
+#ifdef B2_BUILD_PROBES
+  return p.debug_store != 0;
+#else
+  return false;
+#endif
+}
+
 __device__ __forceinline__ long long label_at(const Params& p, long long i) {
   if (p.shift_T <= 0) return p.labels[i];
   return ((i % p.shift_T) + 1 < p.shift_T) ? p.labels[i + 1] : p.ignore_index;
@@ -283,7 +293,9 @@ umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
         const int colbase = nb * BN + half * (BN / 2);
         int nch = (p.N - colbase + 31) / 32;
         nch = nch < 0 ? 0 : (nch > BN / 64 ? BN / 64 : nch);
+#ifdef B2_BUILD_PROBES
         if (MODE == MODE_GEMM && p.c_dtype == 98) nch = 0;     // measurement aid (B2_DEBUG_NOEPI=2): not even the TMEM read
+#endif
         const uint32_t taddr0 = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(as * BN + half * (BN / 2));
         bool released = false;
         auto release = [&]() {                      // one arrival per warp hands the accumulator stage back to the MMA thread
@@ -321,7 +333,9 @@ umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
           // storing modes: this thread's 32 values (one row of the warp's [32 x 32] block) -> 64B-swizzled staging box ->
           // one TMA store per warp
           auto store_block = [&](const float (&v)[32]) {
+#ifdef B2_BUILD_PROBES
             if (p.debug_store == 2) return;          // measurement aid: results are wrong, only the timing means something
+#endif
             uint32_t w[16];
 #pragma unroll
             for (int j = 0; j < 32; j += 2) w[j >> 1] = pack_bf16(v[j], v[j + 1]);
@@ -353,7 +367,7 @@ umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
               if (h == 1 || cc + 1 == nch) {         // block complete (a lone first half: the rest lies beyond the matrix edge)
                 fence_proxy_async_smem();
                 __syncwarp();
-                if (lane_elect && p.debug_store == 0) {
+                if (lane_elect && !probe_skips_store(p)) {
                   tma_store_2d_hint(&tmD, box, colbase + (cc >> 1) * 64, m0 + q * 32, store_policy);
                   bulk_commit();
                 }
@@ -376,9 +390,12 @@ umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
           };
 
           if (MODE == MODE_GEMM) {
+#ifdef B2_BUILD_PROBES
             if (p.c_dtype == 99) {
               // measurement aid (B2_DEBUG_NOEPI=1): accumulator read and discarded, nothing stored
-            } else if (row_ok && p.k_splits > 1) {
+            } else
+#endif
+            if (row_ok && p.k_splits > 1) {
               // split-K: plain fp32 partial tile; splitk_reduce_kernel adds the splits in a fixed order
               float* dst = p.ws + ((long long)t.ks * p.M + row) * p.ldws + col0;     // ldws % 4 == 0, col0 % 32 == 0
               const int ncol = min(32, p.N - col0);
@@ -669,8 +686,12 @@ int num_sms() {
 
 // Shape of the TMA stores of the storing epilogues: [32 x 64] (one per two chunks; default) or [32 x 32] (B2_STORE_BOX=32)
 int debug_store() {
+#ifdef B2_BUILD_PROBES
   static const int v = [] { const char* e = getenv("B2_DEBUG_STORE"); return e == nullptr ? 0 : atoi(e); }();
   return v;
+#else
+  return 0;
+#endif
 }
 // B2_STORE_DIRECT=1: the storing epilogues write global memory straight from registers (A/B against the staged TMA stores)
 int store_direct_env() {
@@ -823,8 +844,10 @@ extern "C" int b2_gemm_bf16(const void* A, int a_mn_major, long long lda, const 
   p.ws = static_cast<float*>(workspace); p.ldws = ((long long)N + 3) / 4 * 4;
   p.C = C; p.ldc = ldc; p.c_dtype = c_dtype; p.accumulate = accumulate;
   // profiling only: mainloop ceiling without the epilogue stores (=1) or without even reading the accumulator (=2)
+#ifdef B2_BUILD_PROBES
   static const int noepi = [] { const char* e = getenv("B2_DEBUG_NOEPI"); return e == nullptr ? 0 : (e[0] == '2' ? 2 : 1); }();
   if (noepi) { p.c_dtype = noepi == 2 ? 98 : 99; p.k_splits = 1; }
+#endif
   if (!a_mn_major && !b_mn_major) rc = launch<MODE_GEMM, 0, 0>(pair, ta, tb, ta, p, stream);
   else if (!a_mn_major && b_mn_major) rc = launch<MODE_GEMM, 0, 1>(pair, ta, tb, ta, p, stream);
   else if (a_mn_major && !b_mn_major) rc = launch<MODE_GEMM, 1, 0>(pair, ta, tb, ta, p, stream);

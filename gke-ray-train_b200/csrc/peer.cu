@@ -372,6 +372,7 @@ extern "C" int b2_peer_slice(size_t n, int dtype, int world, int rank, size_t* b
   return B2_OK;
 }
 
+#ifdef B2_BUILD_PROBES
 // ---------------------------------------------------------------------------------------------------------------------
 // Measurement aid (tools/peer_probe.py, not part of the documented ABI): raw peer copy in one direction with a chosen
 // load flavour, unroll and grid, to find out what the NVLink path sustains from a kernel.
@@ -411,6 +412,8 @@ extern "C" int b2_debug_peer_copy(const void* src, void* dst, size_t bytes, int 
   b2_set_error("b2_debug_peer_copy: unsupported unroll/flavour");
   return B2_ERR_INVALID;
 }
+
+#endif  // B2_BUILD_PROBES
 
 // ---------------------------------------------------------------------------------------------------------------------
 // NVLS variant: the same in-place all-reduce, but the sum over ranks is formed INSIDE the NVSwitch.

@@ -225,10 +225,13 @@ int b2_peer_allgather(void* const* peer_bufs, uint32_t* const* peer_flags, int w
                       size_t n, int dtype, unsigned epoch, int max_blocks, b2_stream_t stream);
 int b2_peer_slice(size_t n, int dtype, int world, int rank, size_t* begin, size_t* end);
 
-/* ---- measurement aid (tools/peer_probe.py; no counterpart in the reference) -----------------------------------
+#ifdef B2_BUILD_PROBES
+/* ---- measurement aid (tools/peer_probe.py; no counterpart in the reference; only in a library built with
+ * -DB2_BUILD_PROBES, i.e. `B2_BUILD_PROBES=1 python gke-ray-train_b200/build.py`) ---------------------------------
  * Raw one-directional copy between a local and a peer-mapped buffer with a chosen load flavour (0 ld.relaxed.sys,
  * 1 plain ld.global, 2 ld.volatile), unroll (1/2/4/8) and grid: what the NVLink path sustains from a kernel. */
 int b2_debug_peer_copy(const void* src, void* dst, size_t bytes, int unroll, int flavour, int blocks, b2_stream_t stream);
+#endif
 
 #ifdef __cplusplus
 }

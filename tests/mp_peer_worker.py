@@ -82,6 +82,7 @@ def main():
             loss.backward()
             b200.clip_grad_norm_(model.parameters(), 0.3)
             opt.step()
+        model.wait_parameters()          # (overlap_param_sync: the last all-gather may still be in flight)
         flat = torch.cat([p.detach().float().reshape(-1) for p in model.parameters()])
         f0 = flat.clone()
         dist.broadcast(f0, 0)

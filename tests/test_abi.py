@@ -19,6 +19,7 @@ def lib():
 def declared_symbols():
     text = open(HEADER).read()
     text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
+    text = re.sub(r"#ifdef B2_BUILD_PROBES.*?#endif", "", text, flags=re.S)     # measurement aids: not in the shipped build
     return sorted(set(re.findall(r"\b(b2_[a-z0-9_]+)\s*\(", text)))
 
 
@@ -153,3 +154,10 @@ def test_without_a_gpu_device_calls_fail_loudly(lib):
     rc = L.b2_symm_alloc(4096, ctypes.byref(p), h)
     assert rc == -2 and L.b2_last_error()                                   # B2_ERR_CUDA, with the driver's reason
     assert L.b2_device_count() <= 0
+
+
+def test_shipped_library_has_no_measurement_aids(lib):
+    """b2_debug_* entry points and the B2_DEBUG_* kernel branches exist only in a -DB2_BUILD_PROBES build."""
+    cdll = ctypes.CDLL(lib.LIB_PATH)
+    assert not hasattr(cdll, "b2_debug_peer_copy")
+    assert "b2_debug_peer_copy" not in lib.EXPORTS

@@ -509,6 +509,34 @@ def test_head_gradient_is_written_into_the_flat_buffer(b200):
             assert float((a.grad.float() - b.grad.float()).norm()) <= 2e-2 * float(b.grad.float().norm()) + 1e-6, n
 
 
+def test_clip_semantics_with_attached_optimizer(b200):
+    """torch's clip_grad_norm_ scales .grad in place (ref: pytorch_llm_ray.py:277). With b200_train.AdamW attached the scale
+    is deferred into the optimizer kernel: (a) defer_to_optimizer=False restores the in-place behaviour; (b) two deferred
+    clips before one step compose like two in-place clips; either way the parameters after step() match torch's."""
+    torch.manual_seed(0)
+    m_ref = nn.Sequential(nn.Linear(64, 64), nn.Tanh(), nn.Linear(64, 8)).to(dev())
+    x = torch.randn(16, 64, device=dev())
+    for mode in ("inplace", "twice"):
+        ref = copy.deepcopy(m_ref); mine = copy.deepcopy(m_ref)
+        o_ref = torch.optim.AdamW(ref.parameters(), lr=1e-2, weight_decay=0.1)
+        o_my = b200.AdamW(mine.parameters(), lr=1e-2, weight_decay=0.1)
+        (ref(x).pow(2).sum() * 50).backward(); (mine(x).pow(2).sum() * 50).backward()
+        if mode == "inplace":
+            n_ref = torch.nn.utils.clip_grad_norm_(ref.parameters(), 1.0)
+            n_my = b200.clip_grad_norm_(mine.parameters(), 1.0, defer_to_optimizer=False)
+            for a, b in zip(mine.parameters(), ref.parameters()):
+                np.testing.assert_allclose(a.grad.cpu().numpy(), b.grad.cpu().numpy(), rtol=2e-5, atol=1e-7)
+        else:
+            torch.nn.utils.clip_grad_norm_(ref.parameters(), 2.0)
+            n_ref = torch.nn.utils.clip_grad_norm_(ref.parameters(), 0.5)
+            b200.clip_grad_norm_(mine.parameters(), 2.0)
+            n_my = b200.clip_grad_norm_(mine.parameters(), 0.5)          # sees the norm AFTER the first clip, like torch
+        np.testing.assert_allclose(n_my.item(), n_ref.item(), rtol=1e-4)
+        o_ref.step(); o_my.step()
+        for a, b in zip(mine.parameters(), ref.parameters()):
+            np.testing.assert_allclose(a.detach().cpu().numpy(), b.detach().cpu().numpy(), rtol=0, atol=2e-6)
+
+
 def test_out_of_range_label_raises_when_asked(b200):
     H = torch.zeros(4, 64, dtype=torch.bfloat16, device=dev()); W = torch.zeros(16, 64, dtype=torch.bfloat16, device=dev())
     y = torch.tensor([[0, 1, 16, 2]], device=dev())

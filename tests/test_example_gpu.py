@@ -41,3 +41,28 @@ def test_example_two_gpus(tmp_path):
         pytest.skip("needs 2 GPUs")
     run_example(tmp_path, "--num-workers", "2")
     run_example(tmp_path, "--num-workers", "2", "--bf16")
+
+
+def run_hf_example(*flags):
+    cmd = [sys.executable, os.path.join(ROOT, "examples", "fine_tune_llama_b200.py"), "--tiny", "--steps", "4"] + list(flags)
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0 and "RESULT" in r.stdout, r.stdout[-2000:] + r.stderr[-3000:]
+    line = [l for l in r.stdout.splitlines() if l.startswith("RESULT")][-1]
+    assert "'loss':" in line and "nan" not in line.lower() and "'step': 4" in line
+    ckpt = line.split("checkpoint:")[1].strip()
+    sd = torch.load(os.path.join(ckpt, "model.pth"), map_location="cpu")
+    assert "lm_head.weight" in sd and "model.embed_tokens.weight" in sd
+    return r.stdout
+
+
+def test_hf_fine_tune_example_single_gpu():
+    """The reference's second job (ref: ray-jobs/fine_tune_llama_ray.py:197-333, HF Trainer's inner loop: accumulation,
+    num_items_in_batch, clip, cosine schedule, model.zero_grad()) through the trainer shim with the fused kernels."""
+    out = run_hf_example("--num-workers", "1")
+    assert "grad_norm" in out
+
+
+def test_hf_fine_tune_example_two_gpus():
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    run_hf_example("--num-workers", "2")

@@ -240,6 +240,10 @@ def test_ce_rows_matches_oracle(ops, dtype, N, V):
     dref = O.cross_entropy_grad(x, y, 1.0 / max(n_valid, 1))
     tol = (O.bf16_ulp(dref) + 1e-7) if dtype == torch.bfloat16 else 1e-6
     assert (np.abs(d - dref) <= tol).all()
+    # the ABI allows the gradient to overwrite the logits (dlogits == logits): same bits as out of place
+    inplace = xt.clone()
+    ops.ce_rows_bwd(inplace, yt, r.lse, gs, out=inplace)
+    assert np.array_equal(inplace.float().cpu().numpy(), d)
 
 
 # ------------------------------------------------------------------------------------------ clip

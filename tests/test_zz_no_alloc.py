@@ -47,6 +47,28 @@ def test_static_scratch_matches_caller_scratch_twice_in_a_row(dtype):
     assert got > 7.5
 
 
+def test_static_scratch_call_leaves_device_memory_untouched():
+    """The one property the entry point exists for: a call takes no device memory. After a warm-up call (the first call on
+    a device resolves the scratch array's address), the driver's free-memory figure and torch's own allocator counters
+    are the same before and after further calls."""
+    from b200_train import _lib
+    torch.cuda.set_device(0)
+    g = (torch.randn(1 << 20, device="cuda") * 0.1).to(torch.bfloat16)
+    out = torch.zeros(1, device="cuda")
+    stream = torch.cuda.current_stream().cuda_stream
+    _lib.call("b2_sumsq_static", g.data_ptr(), g.numel(), _lib.BF16, out.data_ptr(), 0, stream)
+    torch.cuda.synchronize()
+    free0, _ = torch.cuda.mem_get_info()
+    reserved0, allocated0 = torch.cuda.memory_reserved(), torch.cuda.memory_allocated()
+    for _ in range(3):
+        _lib.call("b2_sumsq_static", g.data_ptr(), g.numel(), _lib.BF16, out.data_ptr(), 0, stream)
+    torch.cuda.synchronize()
+    free1, _ = torch.cuda.mem_get_info()
+    assert free1 == free0, (free0, free1)
+    assert (torch.cuda.memory_reserved(), torch.cuda.memory_allocated()) == (reserved0, allocated0)
+    np.testing.assert_allclose(float(out.item()), g.float().double().pow(2).sum().item(), rtol=1e-5)
+
+
 def test_static_scratch_rejects_oversized_input_and_bad_arguments():
     from b200_train import _lib
     L = _lib.lib

@@ -37,6 +37,7 @@ def main():
             e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             e0.record()
             if active:
+                # (a probes build: B2_BUILD_PROBES=1 python gke-ray-train_b200/build.py; B2_LIB=.../build/ab/libb2train_probes.so)
                 rc = _lib.lib.b2_debug_peer_copy(src, dst, nbytes, unroll, flavour, blocks, stream)
                 assert rc == 0, _lib.lib.b2_last_error()
             e1.record(); torch.cuda.synchronize()
