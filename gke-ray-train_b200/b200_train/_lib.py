@@ -61,6 +61,10 @@ _SIGS = {
     "b2_lmhead_ce_bwd_dlogits": (c_int, [c_void_p, c_longlong, c_void_p, c_longlong, c_void_p, c_void_p, c_longlong,
                                          c_longlong, c_int, c_int, c_int, c_longlong, c_int, c_void_p, c_void_p,
                                          c_void_p, c_longlong, c_void_p]),
+    "b2_lmhead_ce_bwd": (c_int, [c_void_p, c_longlong, c_void_p, c_longlong, c_void_p, c_void_p, c_longlong, c_longlong,
+                                 c_int, c_int, c_int, c_longlong, c_int, c_void_p, c_void_p, c_void_p, c_longlong, c_int,
+                                 c_void_p, c_longlong, c_void_p, c_int, c_longlong, c_int, c_void_p, c_int, c_void_p,
+                                 c_size_t, c_void_p]),
     "b2_gemm_bf16": (c_int, [c_void_p, c_int, c_longlong, c_void_p, c_int, c_longlong, c_void_p, c_int, c_longlong,
                              c_int, c_int, c_int, c_int, c_void_p, c_size_t, c_void_p]),
     "b2_gemm_workspace_bytes": (c_size_t, [c_int, c_int]),
@@ -93,7 +97,7 @@ EXPORTS = tuple(_SIGS)
 # number of kernels this process has enqueued through the library (bench.py reports it)
 launch_count = 0
 _LAUNCHES = {"b2_adamw": 1, "b2_adamw_grouped": 1, "b2_sumsq": 1, "b2_sumsq_static": 1, "b2_clip_coef": 1, "b2_scale": 1, "b2_ce_rows_fwd": 2,
-             "b2_ce_rows_bwd": 1, "b2_lmhead_ce_fwd": 3, "b2_lmhead_ce_fwd_keep": 3, "b2_ce_dlogits_inplace": 1, "b2_lmhead_ce_bwd_dlogits": 1, "b2_gather_windows": 1, "b2_gemm_bf16": 1,  # (+1 reduce launch when split-K kicks in)
+             "b2_ce_rows_bwd": 1, "b2_lmhead_ce_fwd": 3, "b2_lmhead_ce_fwd_keep": 3, "b2_ce_dlogits_inplace": 1, "b2_lmhead_ce_bwd_dlogits": 1, "b2_lmhead_ce_bwd": 3, "b2_gather_windows": 1, "b2_gemm_bf16": 1,  # (+1 reduce launch when split-K kicks in)
              "b2_peer_allreduce": 1, "b2_peer_allreduce_mc": 1, "b2_peer_allgather": 1}
 
 

@@ -159,22 +159,17 @@ class _LMHeadCEFn(torch.autograd.Function):
                 dW = direct[0]
             else:
                 dW = torch.empty(V, D, dtype=torch.bfloat16 if n_chunks == 1 else torch.float32, device=H.device)
-        db = torch.zeros(V, dtype=torch.float32, device=H.device) if ctx.has_bias else None
+        db = torch.empty(V, dtype=torch.float32, device=H.device) if ctx.has_bias else None
         for c in range(n_chunks):
             r0 = c * chunk
             rows = min(chunk, N - r0)
-            if kept is not None:        # (single chunk by construction)
-                ops.ce_dlogits_inplace_(dl, labels, lse, gs, r0, rows, V, shift_T=shift_T, ignore_index=ignore_index)
-            else:
-                ops.lmhead_ce_bwd_dlogits(H, W, labels, lse, gs, r0, rows, dl, bias=ctx.bias32, shift_T=shift_T,
-                                          ignore_index=ignore_index, round_logits_bf16=round_bf16)
-            if need_dH:     # dH[rows, D] = dL[rows, V] @ W[V, D]      (B = W read MN-major)
-                ops.gemm_bf16(dl, W, dH[r0:r0 + rows], rows, D, V, a_mn_major=False, b_mn_major=True)
-            if need_dW:     # dW[V, D] += dL^T[V, rows] @ H[rows, D]   (A = dL and B = H both read MN-major)
-                ops.gemm_bf16(dl, H[r0:r0 + rows], dW, V, D, rows, a_mn_major=True, b_mn_major=True,
-                              accumulate=c > 0 or (direct is not None and dW is direct[0] and direct[1]))
-            if db is not None:
-                db += dl[:rows, :V].sum(dim=0, dtype=torch.float32)
+            # one call per chunk: d(logits) (in place from the kept logits, or recomputed), dH, dW, db
+            # dH[rows, D] = dL[rows, V] @ W[V, D];  dW[V, D] += dL^T[V, rows] @ H[rows, D];  db[V] += column sums of dL
+            ops.lmhead_ce_bwd(H, W, labels, lse, gs, r0, rows, dl, kept=kept is not None,
+                              dH=dH[r0:r0 + rows] if need_dH else None, dW=dW if need_dW else None,
+                              dW_accumulate=c > 0 or (direct is not None and dW is direct[0] and direct[1]),
+                              db=db, db_accumulate=c > 0, bias=ctx.bias32, shift_T=shift_T, ignore_index=ignore_index,
+                              round_logits_bf16=round_bf16)
         if direct is not None:
             view, have = direct
             if dW is not view:                       # several chunks: the fp32 sum is rounded once, into the slice

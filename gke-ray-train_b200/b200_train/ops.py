@@ -240,3 +240,32 @@ def gemm_bf16(A, B, C, M, N, K, a_mn_major=False, b_mn_major=False, accumulate=F
              dtype_code(C.dtype), C.stride(0), int(M), int(N), int(K), int(bool(accumulate)), ptr(ws), ws_bytes,
              stream_ptr())
     return C
+
+
+def lmhead_ce_bwd(H, W, labels, lse, gscale, row0, rows, dlogits, *, kept, dH=None, dW=None, dW_accumulate=False, db=None,
+                  db_accumulate=False, bias=None, shift_T=0, ignore_index=-100, round_logits_bf16=True):
+    """The LM-head backward of rows [row0, row0+rows) in one call (b2_lmhead_ce_bwd): d(logits) into `dlogits` (bf16
+    [>= rows, ldd]; with kept=True it holds those rows' kept logits and is rewritten in place), then dH (bf16 [rows, D]),
+    dW (bf16 or fp32 [V, D], optionally accumulated) and db (fp32 [V], optionally accumulated); None skips an output."""
+    _check_hw(H, W, bias)
+    D, V = H.shape[1], W.shape[0]
+    _check_logits_buffer(dlogits, rows, V, H.device)
+    require_cuda(dH, dW, db, lse, gscale, labels)
+    if dH is not None and (dH.dtype != torch.bfloat16 or dH.stride(1) != 1 or dH.shape[0] < rows or dH.shape[1] != D):
+        raise B2Error("lmhead_ce_bwd: dH must be bfloat16 [rows, D] with unit inner stride")
+    if dW is not None and (dW.stride(1) != 1 or tuple(dW.shape) != (V, D)):
+        raise B2Error("lmhead_ce_bwd: dW must be [V, D] with unit inner stride")
+    if db is not None and (db.dtype != torch.float32 or db.numel() != V or not db.is_contiguous()):
+        raise B2Error("lmhead_ce_bwd: db must be a contiguous float32 [V] tensor")
+    Hc = H[row0:row0 + rows]
+    with torch.cuda.device(H.device):
+        ws, ws_bytes = None, 0
+        tiles = ((rows + 127) // 128) * ((D + 255) // 256)
+        if dH is not None and tiles < 3 * 148 and V >= 2048:
+            ws_bytes = _lib.lib.b2_gemm_workspace_bytes(int(rows), int(D))
+            ws = torch.empty(ws_bytes, dtype=torch.uint8, device=H.device)
+        call("b2_lmhead_ce_bwd", ptr(Hc), H.stride(0), ptr(W), W.stride(0), ptr(bias), ptr(labels), int(row0), int(rows),
+             D, V, int(shift_T), int(ignore_index), int(bool(round_logits_bf16)), ptr(lse), ptr(gscale), ptr(dlogits),
+             dlogits.stride(0), int(bool(kept)), ptr(dH), 0 if dH is None else dH.stride(0), ptr(dW),
+             0 if dW is None else dtype_code(dW.dtype), 0 if dW is None else dW.stride(0), int(bool(dW_accumulate)),
+             ptr(db), int(bool(db_accumulate)), ptr(ws), ws_bytes, stream_ptr())

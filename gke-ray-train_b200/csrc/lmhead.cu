@@ -975,3 +975,70 @@ extern "C" int b2_lmhead_ce_bwd_dlogits(const void* H, long long ldh, const void
   p.store_wide = store_wide(); p.debug_store = debug_store(); p.store_direct = store_direct_ok(dlogits, ldd);
   return launch<MODE_CE_BWD, 0, 0>(pair, ta, tb, td, p, stream);
 }
+
+// ---------------------------------------------------------------------------------------------------------------------
+// db[j] (+)= sum over rows of dlogits[r, j]: the bias gradient of an LM head that has one (BasicLLM.fc_out,
+// ref: ray-jobs/pytorch_llm_ray.py:87). One block per 64 columns: 8 threads cover one row's 128 bytes (whole lines), 32
+// rows per pass; the 32 row-groups are then added in a fixed order — no atomics, reproducible.
+namespace {
+__global__ void __launch_bounds__(256) colsum_kernel(const __nv_bfloat16* __restrict__ x, long long ld, long long rows, int V,
+                                                     float* __restrict__ db, int accumulate) {
+  __shared__ float part[32][65];
+  const int cg = threadIdx.x & 7, rg = threadIdx.x >> 3;       // 16-byte column group within the 64 columns; row group
+  const int col0 = blockIdx.x * 64 + cg * 8;
+  float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+  if (col0 < V) {                                               // (ld is a multiple of 8: the vector is inside the row)
+    for (long long r = rg; r < rows; r += 32) {
+      const uint4 u = *reinterpret_cast<const uint4*>(x + r * ld + col0);
+      acc[0] += bf16_lo(u.x); acc[1] += bf16_hi(u.x); acc[2] += bf16_lo(u.y); acc[3] += bf16_hi(u.y);
+      acc[4] += bf16_lo(u.z); acc[5] += bf16_hi(u.z); acc[6] += bf16_lo(u.w); acc[7] += bf16_hi(u.w);
+    }
+  }
+#pragma unroll
+  for (int e = 0; e < 8; ++e) part[rg][cg * 8 + e] = acc[e];
+  __syncthreads();
+  if (threadIdx.x < 64) {
+    const int col = blockIdx.x * 64 + threadIdx.x;
+    if (col < V) {
+      float s = 0.f;
+      for (int g = 0; g < 32; ++g) s += part[g][threadIdx.x];
+      db[col] = s + (accumulate ? db[col] : 0.f);
+    }
+  }
+}
+}  // namespace
+
+// The whole LM-head backward for a chunk of rows behind one call (the entry SURVEY.md §8(b) proposed): d(logits) into
+// `dlogits` (transformed in place from kept logits when kept != 0, recomputed on the tensor cores otherwise), then
+// dH = dlogits @ W, dW (+)= dlogits^T @ H and, for a head with a bias, db (+)= column sums — all enqueued on `stream`.
+extern "C" int b2_lmhead_ce_bwd(const void* H, long long ldh, const void* W, long long ldw, const float* bias,
+                                const long long* labels, long long row0, long long rows, int D, int V, int shift_T,
+                                long long ignore_index, int round_logits_bf16, const float* lse, const float* gscale_dev,
+                                void* dlogits, long long ldd, int kept, void* dH, long long lddh, void* dW, int dw_dtype,
+                                long long lddw, int dw_accumulate, float* db, int db_accumulate, void* gemm_workspace,
+                                size_t gemm_workspace_bytes, cudaStream_t stream) {
+  if (rows == 0) return B2_OK;
+  B2_REQUIRE(dlogits != nullptr, "b2_lmhead_ce_bwd: null dlogits buffer");
+  int rc;
+  if (kept) rc = b2_ce_dlogits_inplace(dlogits, ldd, labels, row0, rows, V, shift_T, ignore_index, lse, gscale_dev, stream);
+  else rc = b2_lmhead_ce_bwd_dlogits(H, ldh, W, ldw, bias, labels, row0, rows, D, V, shift_T, ignore_index,
+                                     round_logits_bf16, lse, gscale_dev, dlogits, ldd, stream);
+  if (rc != B2_OK) return rc;
+  B2_REQUIRE(rows < (1ll << 31), "b2_lmhead_ce_bwd: too many rows");
+  if (dH != nullptr) {        // dH[rows, D] = dL[rows, V] @ W[V, D]          (B = W read MN-major)
+    const bool ws_ok = gemm_workspace != nullptr && gemm_workspace_bytes >= b2_gemm_workspace_bytes((int)rows, D);
+    rc = b2_gemm_bf16(dlogits, 0, ldd, W, 1, ldw, dH, B2_BF16, lddh, (int)rows, D, V, 0, ws_ok ? gemm_workspace : nullptr,
+                      ws_ok ? gemm_workspace_bytes : 0, stream);
+    if (rc != B2_OK) return rc;
+  }
+  if (dW != nullptr) {        // dW[V, D] (+)= dL^T[V, rows] @ H[rows, D]      (A = dL and B = H both read MN-major)
+    rc = b2_gemm_bf16(dlogits, 1, ldd, H, 1, ldh, dW, dw_dtype, lddw, V, D, (int)rows, dw_accumulate, nullptr, 0, stream);
+    if (rc != B2_OK) return rc;
+  }
+  if (db != nullptr) {
+    colsum_kernel<<<(unsigned)((V + 63) / 64), 256, 0, stream>>>(static_cast<const __nv_bfloat16*>(dlogits), ldd, rows, V, db,
+                                                               db_accumulate);
+    B2_CHECK_CUDA(cudaGetLastError());
+  }
+  return B2_OK;
+}

@@ -154,6 +154,23 @@ int b2_lmhead_ce_bwd_dlogits(const void* H, long long ldh, const void* W, long l
                              const long long* labels, long long row0, long long rows, int D, int V, int shift_T,
                              long long ignore_index, int round_logits_bf16, const float* lse,
                              const float* gscale_dev, void* dlogits, long long ldd, b2_stream_t stream);
+/* The LM-head backward of a chunk of rows behind ONE call — replaces `loss.backward()` through ForCausalLMLoss and
+ * lm_head (ref: ray-jobs/pytorch_llm_ray.py:276; $SP/transformers/loss/loss_utils.py:28-67 and the autograd of
+ * nn.Linear at $SP/transformers/models/llama/modeling_llama.py:486; bias: BasicLLM.fc_out, ref :87). Enqueues, in order:
+ *   d(logits) for rows [row0, row0+rows) into `dlogits` (bf16 [rows, ldd]): kept != 0 — `dlogits` holds the logits that
+ *     b2_lmhead_ce_fwd_keep left for these rows and is rewritten in place (b2_ce_dlogits_inplace); kept == 0 — recomputed
+ *     on the tensor cores (b2_lmhead_ce_bwd_dlogits);
+ *   dH [rows, lddh] bf16 = dlogits @ W                     (skipped when dH is NULL);
+ *   dW [V, lddw] (dw_dtype f32 / bf16) = or += dlogits^T @ H   (skipped when dW is NULL; dw_accumulate != 0 adds);
+ *   db [V] fp32 = or += column sums of dlogits              (skipped when db is NULL; fixed summation order).
+ * H points at row row0 of the hidden states; labels and lse are the full arrays. gemm_workspace (optional):
+ * b2_gemm_workspace_bytes(rows, D) bytes that let the dH GEMM split K. */
+int b2_lmhead_ce_bwd(const void* H, long long ldh, const void* W, long long ldw, const float* bias,
+                     const long long* labels, long long row0, long long rows, int D, int V, int shift_T,
+                     long long ignore_index, int round_logits_bf16, const float* lse, const float* gscale_dev,
+                     void* dlogits, long long ldd, int kept, void* dH, long long lddh, void* dW, int dw_dtype,
+                     long long lddw, int dw_accumulate, float* db, int db_accumulate, void* gemm_workspace,
+                     size_t gemm_workspace_bytes, b2_stream_t stream);
 /* Plain bf16 GEMM on the same tcgen05 mainloop: C[M,N] (+)= A[M,K] * B[N,K]^T, fp32 accumulate.
  * a_mn_major = 0: A stored [M, lda] with K contiguous; 1: A stored [K, lda] with M contiguous. Same for B
  * with N. C row-major [M, ldc], fp32 or bf16; accumulate != 0 adds to the existing C.

@@ -246,6 +246,43 @@ def test_ce_rows_matches_oracle(ops, dtype, N, V):
     assert np.array_equal(inplace.float().cpu().numpy(), d)
 
 
+@pytest.mark.parametrize("kept", [False, True])
+@pytest.mark.parametrize("N,D,V,shift_T", [(256, 128, 520, 0), (300, 64, 283, 10), (640, 256, 1031, 64)])
+def test_lmhead_ce_bwd_one_call_matches_oracle_gradients(ops, N, D, V, shift_T, kept):
+    """b2_lmhead_ce_bwd: d(logits), dH, dW and the bias gradient db behind one entry point, from kept logits and by
+    recompute, against the oracle's d(logits) pushed through fp64 matrix products; a second call accumulates dW / db."""
+    rng = np.random.default_rng(N * 3 + V)
+    H, Ht = bf16_tensor(rng, (N, D))
+    W, Wt = bf16_tensor(rng, (V, D), scale=2.0 / np.sqrt(D))
+    b = (rng.standard_normal(V) * 0.1).astype(np.float32)
+    bt = torch.from_numpy(b).to(dev())
+    y = make_labels(rng, N, V)
+    yt = torch.from_numpy(y).to(dev())
+    ldd = (V + 63) // 64 * 64
+    dl = torch.full((N, ldd), float("nan"), dtype=torch.bfloat16, device=dev())
+    r = ops.lmhead_ce_fwd(Ht, Wt, yt, bias=bt, shift_T=shift_T, keep_logits=dl if kept else None)
+    gs = torch.tensor([0.5 / N], dtype=torch.float32, device=dev())
+    dH = torch.empty(N, D, dtype=torch.bfloat16, device=dev())
+    dW = torch.empty(V, D, dtype=torch.float32, device=dev())
+    db = torch.full((V,), float("nan"), dtype=torch.float32, device=dev())
+    ops.lmhead_ce_bwd(Ht, Wt, yt, r.lse, gs, 0, N, dl, kept=kept, dH=dH, dW=dW, db=db, bias=bt, shift_T=shift_T)
+    o = O.lmhead_ce(H, W, y, bias=b, shift_T=shift_T, bf16_logits=True)
+    d = O.bf16_round(O.cross_entropy_grad(o["logits"], o["labels"], 0.5 / N)).astype(np.float64)
+    want_dH, want_dW, want_db = d @ W.astype(np.float64), d.T @ H.astype(np.float64), d.sum(axis=0)
+    got = dl[:, :V].float().cpu().numpy()
+    assert (np.abs(got - d) <= O.bf16_ulp(d.astype(np.float32)) + 2e-6).all()
+    for g, w, name in ((dH.float().cpu().numpy(), want_dH, "dH"), (dW.cpu().numpy(), want_dW, "dW"), (db.cpu().numpy(), want_db, "db")):
+        rel = np.linalg.norm(g - w) / max(np.linalg.norm(w), 1e-30)
+        assert np.isfinite(g).all() and rel < 1e-2, f"{name}: relative error {rel:.3e}"
+    np.testing.assert_allclose(db.cpu().numpy(), got.astype(np.float64).sum(axis=0), rtol=1e-5, atol=1e-7)   # exact sums of the stored values
+    # accumulate: the same chunk again on top (recompute route, the kept logits are gone)
+    dW2, db2 = dW.clone(), db.clone()
+    ops.lmhead_ce_bwd(Ht, Wt, yt, r.lse, gs, 0, N, dl, kept=False, dW=dW2, dW_accumulate=True, db=db2, db_accumulate=True,
+                      bias=bt, shift_T=shift_T)
+    np.testing.assert_allclose(dW2.cpu().numpy(), 2 * dW.cpu().numpy(), rtol=1e-5, atol=1e-8)
+    np.testing.assert_allclose(db2.cpu().numpy(), 2 * db.cpu().numpy(), rtol=1e-5, atol=1e-8)
+
+
 # ------------------------------------------------------------------------------------------ clip
 @pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
 @pytest.mark.parametrize("n", [1, 7, 8, 1000, 1 << 20, (1 << 22) + 13])
