@@ -151,6 +151,8 @@ class DistributedDataParallel(nn.Module):
                 buf.after_shard_update = self._make_shard_sync(buf)
                 buf.param_gate = self._make_param_gate(buf)
         self._next_bucket = 0
+        # B2_DDP_TRACE=1: CUDA events around every bucket launch of a backward pass (trace_report() reads them)
+        self._trace = [] if os.environ.get("B2_DDP_TRACE") == "1" else None
         self._comm_stream = torch.cuda.Stream(device=device) if self.overlap else None
         self._ag_pending = {}
         for p in params:
@@ -173,15 +175,29 @@ class DistributedDataParallel(nn.Module):
         mode = 1 if first else 2          # sum-of-squares slots: restart on a buffer's first bucket, then keep adding
         kw = dict(want_sumsq=mode, offset=b.offset, numel=b.numel, scatter_only=self.shard_optimizer,
                   sumsq_out=b.buf._sumsq_store if last_of_buf else None)
+        tr = None
+        if self._trace is not None:
+            tr = {"key": b.key, "mb": b.numel * b.buf.data.element_size() / 2 ** 20, "tail": bool(tail),
+                  "ready": torch.cuda.Event(enable_timing=True), "start": torch.cuda.Event(enable_timing=True),
+                  "end": torch.cuda.Event(enable_timing=True)}
+            self._trace.append(tr)
         if self.overlap:
-            ev = torch.cuda.Event()
+            ev = tr["ready"] if tr else torch.cuda.Event()
             ev.record(torch.cuda.current_stream())
             self._comm_stream.wait_event(ev)
             with torch.cuda.stream(self._comm_stream):
+                if tr:
+                    tr["start"].record()
                 # tail: nothing left to overlap with -> whole GPU
                 self.comm.allreduce_(b.buf.grad, max_blocks=0 if tail else self._overlap_blocks, **kw)
+                if tr:
+                    tr["end"].record()
         else:
+            if tr:
+                tr["ready"].record(); tr["start"].record()
             self.comm.allreduce_(b.buf.grad, **kw)
+            if tr:
+                tr["end"].record()
         if last_of_buf:
             b.buf.reduced_sumsq = b.buf._sumsq_store
 
@@ -220,12 +236,38 @@ class DistributedDataParallel(nn.Module):
         launch order are the ones the overlapped path uses)."""
         for buf in self.flat_buffers:
             buf.install_grads()            # parameters that received no gradient contribute zeros
+        if self._trace is not None:
+            self._trace_bwd_end = torch.cuda.Event(enable_timing=True)
+            self._trace_bwd_end.record()
         self._launch_ready(force=True)     # whatever is left (all of it without overlap; unused parameters' buckets)
         if self.overlap:
             torch.cuda.current_stream().wait_stream(self._comm_stream)
+        if self._trace is not None:
+            self._trace_joined = torch.cuda.Event(enable_timing=True)
+            self._trace_joined.record()
         self._next_bucket = 0
         for b in self._buckets:
             b.pending = b.nparams
+
+    def trace_report(self):
+        """B2_DDP_TRACE=1: timeline of the LAST backward pass's bucket launches, in ms relative to the moment the first
+        bucket became ready — when each bucket's last gradient had landed (`ready`), when its kernel started and ended on
+        the side stream, whether it ran as tail (after backward, whole GPU), when backward ended and when the main
+        stream had joined the side stream (`exposed_ms` = joined - backward end: communication nothing could hide)."""
+        if not self._trace:
+            return None
+        torch.cuda.synchronize()
+        n = len(self._buckets)
+        last = self._trace[-n:]
+        t0 = last[0]["ready"]
+        out = {"buckets": [{"bucket": t["key"], "MiB": round(t["mb"], 1), "tail": t["tail"],
+                            "ready_ms": round(t0.elapsed_time(t["ready"]), 3), "start_ms": round(t0.elapsed_time(t["start"]), 3),
+                            "end_ms": round(t0.elapsed_time(t["end"]), 3)} for t in last],
+               "backward_end_ms": round(t0.elapsed_time(self._trace_bwd_end), 3),
+               "joined_ms": round(t0.elapsed_time(self._trace_joined), 3)}
+        out["exposed_ms"] = round(out["joined_ms"] - out["backward_end_ms"], 3)
+        self._trace.clear()
+        return out
 
     # ------------------------------------------------------------------ sharded optimizer: parameter all-gather
     def _make_shard_sync(self, buf):
