@@ -4,9 +4,9 @@ cd "$GRAFT_REPO_ROOT" 2>/dev/null || cd /root/repo
 mkdir -p gpurun_out
 timeout 420 python -m pytest tests/test_multigpu.py -m gpu -x -q -k "8" > gpurun_out/r2c8_mgpu.log 2>&1; echo "mgpu rc=$?"; tail -4 gpurun_out/r2c8_mgpu.log
 TR="python -m torch.distributed.run --nnodes=1 --nproc-per-node 8 --master-addr 127.0.0.1 --master-port 29518"
-timeout 240 $TR bench.py --gpus 8 --steps 20 --warmup 5 > gpurun_out/r2c8_gpt2_n8.log 2>&1; echo "gpt2 rc=$?"; tail -1 gpurun_out/r2c8_gpt2_n8.log | cut -c1-160
+B2_DDP_TRACE=1 timeout 240 $TR bench.py --gpus 8 --steps 20 --warmup 5 > gpurun_out/r2c8_gpt2_n8.log 2>&1; echo "gpt2 rc=$?"; tail -1 gpurun_out/r2c8_gpt2_n8.log | cut -c1-160
 for v in 0 2; do
-  timeout 300 $TR bench.py --gpus 8 --steps 20 --warmup 5 --workload llama-1b --shard-optimizer $v --no-f2-large > gpurun_out/r2c8_l1b_n8_shard$v.log 2>&1; echo "l1b shard$v rc=$?"; tail -1 gpurun_out/r2c8_l1b_n8_shard$v.log | cut -c1-160
+  B2_DDP_TRACE=1 timeout 300 $TR bench.py --gpus 8 --steps 20 --warmup 5 --workload llama-1b --shard-optimizer $v --no-f2-large > gpurun_out/r2c8_l1b_n8_shard$v.log 2>&1; echo "l1b shard$v rc=$?"; tail -1 gpurun_out/r2c8_l1b_n8_shard$v.log | cut -c1-160
 done
 for v in 2 0; do
   timeout 420 $TR bench.py --gpus 8 --steps 20 --warmup 5 --workload llama-8b --shard-optimizer $v --no-f2-large > gpurun_out/r2c8_l8b_n8_shard$v.log 2>&1; echo "l8b shard$v rc=$?"; tail -1 gpurun_out/r2c8_l8b_n8_shard$v.log | cut -c1-160
