@@ -269,21 +269,25 @@ def f2_parity_check(torch, dist, model, optimizer, ops, batch, B):
     optimizer.zero_grad(set_to_none=True)
     with model.no_sync():
         model(input_ids=ids[:B], labels=lab[:B]).loss.backward()
-    res = {"f2": "ok", "max_ulp": 0.0, "kernel": None, "identical_across_ranks": True, "sumsq_rel_err": 0.0,
+    res = {"f2": "ok", "max_ulp": 0.0, "max_err_over_tol": 0.0, "kernel": None, "identical_across_ranks": True, "sumsq_rel_err": 0.0,
            "sharded": bool(model.shard_optimizer), "buckets": len(model._buckets)}
     CH = 1 << 26                                           # elements per piece: the checker must not need GBs of its own
     refs = []
     for buf in model.flat_buffers:
         buf.install_grads()
         ref = torch.empty_like(buf.grad)
+        mag = torch.empty_like(buf.grad)                   # mean over ranks of |g|: the scale of the fp32 summation error
         for a in range(0, buf.numel, CH):
             piece = buf.grad[a:a + CH].float()
+            absp = piece.abs()
             dist.all_reduce(piece)                         # NCCL: the checker
+            dist.all_reduce(absp)
             ref[a:a + CH] = (piece * (1.0 / world)).to(buf.dtype)
-        refs.append(ref)
+            mag[a:a + CH] = (absp * (1.0 / world)).to(buf.dtype)
+        refs.append((ref, mag))
     model.reduce_gradients()
     torch.cuda.synchronize()
-    for buf, ref in zip(model.flat_buffers, refs):
+    for buf, (ref, mag) in zip(model.flat_buffers, refs):
         res["kernel"] = model.comm.kernel_name(buf.grad)
         segs = [(lo, hi) for lo, hi, _ in buf.shards] if buf.shards is not None else [(0, buf.numel)]
         mant_bits = 8 if buf.dtype == torch.bfloat16 else 24
@@ -294,7 +298,11 @@ def f2_parity_check(torch, dist, model, optimizer, ops, batch, B):
                 b = min(a + CH, hi)
                 got, want = buf.grad[a:b].float(), ref[a:b].float()
                 ulp = torch.ldexp(torch.ones_like(want), torch.frexp(want.abs().clamp_min(1e-30))[1] - mant_bits)
+                # one rounding of the result, plus what a different fp32 summation ORDER can move the sum by when the
+                # addends cancel (the sum is far smaller than they are): W fp32 roundings at the addends' magnitude
+                slack = mag[a:b].float() * (world * 2.0 ** -23)
                 res["max_ulp"] = max(res["max_ulp"], float(((got - want).abs() / ulp).max()))
+                res["max_err_over_tol"] = max(res["max_err_over_tol"], float(((got - want).abs() / (ulp + slack)).max()))
                 chk += buf.grad[a:b].view(torch.int16 if buf.dtype == torch.bfloat16 else torch.int32).to(torch.int64).sum()
             if hi > lo:
                 direct += float(ops.sumsq(buf.grad[lo:hi]).item())
@@ -307,10 +315,12 @@ def f2_parity_check(torch, dist, model, optimizer, ops, batch, B):
             fused = float(buf.reduced_sumsq[rank])
         res["sumsq_rel_err"] = max(res["sumsq_rel_err"], abs(fused - direct) / max(direct, 1e-30))
     del refs
-    # W = 2: the fp32 sum of two values is exact, so the kernels must agree with NCCL bit for bit; W > 2: summation order
-    # (ours: rank order; NVLS: inside the switch; NCCL: ring) may differ by one rounding of the result
-    tol = 0.0 if world == 2 else (1.0 if all(b.dtype == torch.bfloat16 for b in model.flat_buffers) else 4.0)
-    ok = res["max_ulp"] <= tol and res["identical_across_ranks"] and res["sumsq_rel_err"] < 1e-4
+    # W = 2: the fp32 sum of two values is exact, so the kernels must agree with NCCL bit for bit (max_ulp == 0). W > 2:
+    # the summation order differs (ours: rank order; NVLS: inside the switch; NCCL: ring), so the bound is one rounding
+    # of the result plus the fp32 reassociation error at the magnitude of the addends (max_err_over_tol <= 1); max_ulp,
+    # measured at the magnitude of the RESULT, is reported too and exceeds 1 only where the ranks' gradients cancel
+    ok = (res["max_ulp"] == 0.0 if world == 2 else res["max_err_over_tol"] <= 1.0) \
+        and res["identical_across_ranks"] and res["sumsq_rel_err"] < 1e-4
     flag = torch.tensor([0 if ok else 1], device=ids.device)
     dist.all_reduce(flag)
     if int(flag):
@@ -487,7 +497,6 @@ def run_ours(args):
             raise SystemExit(3)
         step(*resident[0])                                  # back to a normal step before timing
         torch.cuda.synchronize()
-    torch.cuda.empty_cache()
     torch.cuda.reset_peak_memory_stats(device)             # peak memory of the timed steps, not of the checker above
 
     sampler = ClockSampler(local_rank) if rank == 0 else None
