@@ -233,7 +233,7 @@ def gemm_bf16(A, B, C, M, N, K, a_mn_major=False, b_mn_major=False, accumulate=F
     with torch.cuda.device(A.device):
         ws, ws_bytes = None, 0
         tiles = ((M + 127) // 128) * ((N + 255) // 256)
-        if split_k and tiles < 3 * 148 and K >= 2048:
+        if split_k and tiles < 12 * 148 and K >= 2048:
             ws_bytes = _lib.lib.b2_gemm_workspace_bytes(int(M), int(N))
             ws = torch.empty(ws_bytes, dtype=torch.uint8, device=A.device)
         call("b2_gemm_bf16", ptr(A), int(a_mn_major), A.stride(0), ptr(B), int(b_mn_major), B.stride(0), ptr(C),
@@ -261,7 +261,7 @@ def lmhead_ce_bwd(H, W, labels, lse, gscale, row0, rows, dlogits, *, kept, dH=No
     with torch.cuda.device(H.device):
         ws, ws_bytes = None, 0
         tiles = ((rows + 127) // 128) * ((D + 255) // 256)
-        if dH is not None and tiles < 3 * 148 and V >= 2048:
+        if dH is not None and tiles < 12 * 148 and V >= 2048:
             ws_bytes = _lib.lib.b2_gemm_workspace_bytes(int(rows), int(D))
             ws = torch.empty(ws_bytes, dtype=torch.uint8, device=H.device)
         call("b2_lmhead_ce_bwd", ptr(Hc), H.stride(0), ptr(W), W.stride(0), ptr(bias), ptr(labels), int(row0), int(rows),

@@ -402,8 +402,8 @@ umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
 #pragma unroll
               for (int j = 0; j < 32; j += 4)
                 if (j < ncol)
-                  *reinterpret_cast<float4*>(dst + j) = make_float4(__uint_as_float(r[j]), __uint_as_float(r[j + 1]),
-                                                                    __uint_as_float(r[j + 2]), __uint_as_float(r[j + 3]));
+                  __stcs(reinterpret_cast<float4*>(dst + j), make_float4(__uint_as_float(r[j]), __uint_as_float(r[j + 1]),
+                                                                         __uint_as_float(r[j + 2]), __uint_as_float(r[j + 3])));
             } else if (row_ok) {
               const int ncol = min(32, p.N - col0);
               if (p.c_dtype == B2_F32) {
@@ -413,7 +413,9 @@ umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
                   for (int j = 0; j < 32; j += 4) {
                     float4 v = make_float4(__uint_as_float(r[j]), __uint_as_float(r[j + 1]), __uint_as_float(r[j + 2]), __uint_as_float(r[j + 3]));
                     if (p.accumulate) { const float4 o = *reinterpret_cast<const float4*>(dst + j); v.x += o.x; v.y += o.y; v.z += o.z; v.w += o.w; }
-                    *reinterpret_cast<float4*>(dst + j) = v;
+                    // streaming store: the output is written once and must not push the operand tiles (re-read by every
+                    // unit of the wave) out of L2
+                    __stcs(reinterpret_cast<float4*>(dst + j), v);
                   }
                 } else {
 #pragma unroll
@@ -433,7 +435,7 @@ umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
                       v[0] += bf16_lo(o.x); v[1] += bf16_hi(o.x); v[2] += bf16_lo(o.y); v[3] += bf16_hi(o.y);
                       v[4] += bf16_lo(o.z); v[5] += bf16_hi(o.z); v[6] += bf16_lo(o.w); v[7] += bf16_hi(o.w);
                     }
-                    *reinterpret_cast<uint4*>(dst + j) = make_uint4(pack_bf16(v[0], v[1]), pack_bf16(v[2], v[3]), pack_bf16(v[4], v[5]), pack_bf16(v[6], v[7]));
+                    __stcs(reinterpret_cast<uint4*>(dst + j), make_uint4(pack_bf16(v[0], v[1]), pack_bf16(v[2], v[3]), pack_bf16(v[4], v[5]), pack_bf16(v[6], v[7])));
                   }
                 } else {
 #pragma unroll
@@ -800,7 +802,7 @@ int choose_splits(int num_m_blocks, int num_n_blocks, int grid) {
 
 // split-K factor for a plain GEMM: used when the output has too few 128x256 tiles to fill the 148 SMs
 static int auto_k_splits(int tiles, int num_k_blocks, int sms) {
-  if (tiles >= 3 * sms || num_k_blocks < 32) return 1;
+  if (tiles >= 6 * sms || num_k_blocks < 32) return 1;
   // units are dealt round-robin to `sms` persistent CTAs: pick the smallest split whose last wave is nearly full
   int best = 1; double best_eff = 0.0;
   for (int ks = 1; ks <= B2_GEMM_MAX_KSPLIT; ++ks) {
