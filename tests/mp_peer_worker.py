@@ -118,9 +118,11 @@ def main():
         assert torch.equal(sd["state"][k]["exp_avg_sq"], sd_s["state"][k]["exp_avg_sq"]), k
     # optimizer memory is really sharded
     full = sum(b.numel for b in opt.flat_buffers()); part = sum(b.exp_avg.numel() for b in opt_s.flat_buffers())
-    # (slices are 64-element aligned per bucket, so the ranks' shares differ by at most 64 elements per bucket)
+    # (slices are 64-element aligned per bucket: the first W-1 ranks round their share up, the last one takes the rest,
+    # so a rank's share is within 64 * W elements per bucket of full / W)
     tot = torch.tensor([part], device=dev, dtype=torch.int64); dist.all_reduce(tot)
-    assert int(tot) == full and abs(part * world - full) <= 64 * world * len(model_s._buckets), (part, full)
+    assert int(tot) == full, (int(tot), full)
+    assert abs(part * world - full) <= 64 * world * world * len(model_s._buckets), (part, full)
     model_s.close()
     # --- gradient accumulation: two micro-batches, the first under no_sync() (ref: fine_tune_config.json:14)
     torch.manual_seed(7)
