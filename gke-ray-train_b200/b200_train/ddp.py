@@ -153,7 +153,11 @@ class DistributedDataParallel(nn.Module):
         self._next_bucket = 0
         # B2_DDP_TRACE=1: CUDA events around every bucket launch of a backward pass (trace_report() reads them)
         self._trace = [] if os.environ.get("B2_DDP_TRACE") == "1" else None
-        self._comm_stream = torch.cuda.Stream(device=device) if self.overlap else None
+        # the side stream outranks the compute stream (B2_DDP_STREAM_PRIORITY, default -1 = high): a bucket's CTAs are placed
+        # as soon as SM slots free up instead of after the backward kernels queued at that moment, so the exchange starts
+        # (and every rank reaches its start barrier) when the bucket is ready, not a few kernels later
+        prio = int(os.environ.get("B2_DDP_STREAM_PRIORITY", "-1"))
+        self._comm_stream = torch.cuda.Stream(device=device, priority=prio) if self.overlap else None
         self._ag_pending = {}
         for p in params:
             p.register_post_accumulate_grad_hook(self._on_grad)
