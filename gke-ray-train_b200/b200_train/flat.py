@@ -9,6 +9,11 @@ prepare_model installs for the reference (ref: ray-jobs/pytorch_llm_ray.py:230).
 """
 import torch
 
+import os
+
+# measurement aid (tools/host_bound_probe.py): leave the gradients where autograd put them until install_grads() runs
+_LAND_LATE = os.environ.get("B2_LAND_LATE") == "1"
+
 ALIGN = 64  # elements; every parameter starts on a 64-element boundary (>= 128 B), padding stays zero
 # The buffer length is a multiple of 64 * lcm(1..8) elements, so that for any world size up to 8 the per-rank slices of
 # the peer-memory collectives (and of a sharded optimizer) are equal-sized and start on 64-element boundaries.
@@ -72,6 +77,8 @@ class FlatBuffer:
         (Zero-filling the buffer up front and letting autograd add into it costs a fill plus a read-modify-write: four
         passes over the gradients instead of two.) Later micro-batches of an accumulation find .grad already pointing
         into the buffer and autograd adds in place."""
+        if _LAND_LATE:
+            return
         i = self._index.get(id(p))
         if i is None:                          # a copy of one of our parameters that inherited the hook: not ours
             return
