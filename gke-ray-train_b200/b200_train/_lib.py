@@ -68,6 +68,7 @@ _SIGS = {
     "b2_gemm_bf16": (c_int, [c_void_p, c_int, c_longlong, c_void_p, c_int, c_longlong, c_void_p, c_int, c_longlong,
                              c_int, c_int, c_int, c_int, c_void_p, c_size_t, c_void_p]),
     "b2_gemm_workspace_bytes": (c_size_t, [c_int, c_int]),
+    "b2_land_copy": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_void_p, c_void_p]),
     "b2_gather_windows": (c_int, [c_void_p, c_longlong, c_void_p, c_int, c_int, c_void_p, c_void_p, c_void_p, c_void_p]),
     "b2_peer_flags_bytes": (c_size_t, []),
     "b2_symm_alloc": (c_int, [c_size_t, c_void_p, c_void_p]),
@@ -97,7 +98,7 @@ EXPORTS = tuple(_SIGS)
 # number of kernels this process has enqueued through the library (bench.py reports it)
 launch_count = 0
 _LAUNCHES = {"b2_adamw": 1, "b2_adamw_grouped": 1, "b2_sumsq": 1, "b2_sumsq_static": 1, "b2_clip_coef": 1, "b2_scale": 1, "b2_ce_rows_fwd": 2,
-             "b2_ce_rows_bwd": 1, "b2_lmhead_ce_fwd": 3, "b2_lmhead_ce_fwd_keep": 3, "b2_ce_dlogits_inplace": 1, "b2_lmhead_ce_bwd_dlogits": 1, "b2_lmhead_ce_bwd": 3, "b2_gather_windows": 1, "b2_gemm_bf16": 1,  # (+1 reduce launch when split-K kicks in)
+             "b2_ce_rows_bwd": 1, "b2_lmhead_ce_fwd": 3, "b2_lmhead_ce_fwd_keep": 3, "b2_ce_dlogits_inplace": 1, "b2_lmhead_ce_bwd_dlogits": 1, "b2_lmhead_ce_bwd": 3, "b2_gather_windows": 1, "b2_land_copy": 1, "b2_gemm_bf16": 1,  # (+1 reduce launch when split-K kicks in)
              "b2_peer_allreduce": 1, "b2_peer_allreduce_mc": 1, "b2_peer_allgather": 1}
 
 

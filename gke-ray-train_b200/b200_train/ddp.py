@@ -175,6 +175,7 @@ class DistributedDataParallel(nn.Module):
         the side stream, ordered after everything the backward stream has enqueued so far, on a capped grid so it shares
         the SMs with the remaining backward kernels. The launch that completes a buffer also delivers the W per-rank
         sums of squares (its last act, after the end barrier) into the buffer's own store."""
+        b.buf.flush_landing()             # gradients still waiting in their own allocations move into the buffer first
         first = self._next_bucket == 0 or b.buf is not self._buckets[self._next_bucket - 1].buf
         mode = 1 if first else 2          # sum-of-squares slots: restart on a buffer's first bucket, then keep adding
         kw = dict(want_sumsq=mode, offset=b.offset, numel=b.numel, scatter_only=self.shard_optimizer,

@@ -13,6 +13,9 @@ import os
 
 # measurement aid (tools/host_bound_probe.py): leave the gradients where autograd put them until install_grads() runs
 _LAND_LATE = os.environ.get("B2_LAND_LATE") == "1"
+# gradients that wait in their own allocations are moved into the flat buffer once this many bytes have gathered (bounds
+# the extra memory; B2_LAND_FLUSH_MB=0 copies each one at once, the round-2 behaviour before the gather kernel)
+_LAND_FLUSH_BYTES = int(float(os.environ.get("B2_LAND_FLUSH_MB", "64")) * (1 << 20))
 
 ALIGN = 64  # elements; every parameter starts on a 64-element boundary (>= 128 B), padding stays zero
 # The buffer length is a multiple of 64 * lcm(1..8) elements, so that for any world size up to 8 the per-rank slices of
@@ -46,6 +49,7 @@ class FlatBuffer:
                 p._b2_flat = (self, o)
         self._views = None
         self._index = {id(p): i for i, p in enumerate(self.params)}
+        self._stolen, self._stolen_bytes, self._stolen_set = [], 0, set()   # gradients waiting for the next b2_land_copy launch
         for i, p in enumerate(self.params):
             if p.grad is not None:             # a gradient that already exists moves into the buffer; none stays none
                 self.grad_view(i).copy_(p.grad)
@@ -73,7 +77,9 @@ class FlatBuffer:
     def _land(self, p):
         """Post-accumulate-grad hook. After `zero_grad(set_to_none=True)` (ours, the model's, HF Trainer's) a parameter
         has no .grad, so autograd hands over the freshly computed gradient tensor instead of adding it to something; here
-        that tensor is copied into the parameter's slice of the flat buffer — one read and one write — and released.
+        that tensor is copied into the parameter's slice of the flat buffer — one read and one write — and released;
+        the copies are gathered: a gradient waits in its own allocation until 64 MB have accumulated (or someone needs the
+        buffer) and one b2_land_copy launch then moves them all, instead of one small copy kernel per parameter.
         (Zero-filling the buffer up front and letting autograd add into it costs a fill plus a read-modify-write: four
         passes over the gradients instead of two.) Later micro-batches of an accumulation find .grad already pointing
         into the buffer and autograd adds in place."""
@@ -86,15 +92,51 @@ class FlatBuffer:
         g = p.grad
         if g is want:
             return
-        if g is not None and g.data_ptr() != want.data_ptr():
+        if g is None or g.data_ptr() == want.data_ptr():
+            p.grad = want
+            return
+        if (g.is_cuda and g.dtype == self.dtype and g.is_contiguous() and g.data_ptr() % 16 == 0
+                and g.numel() == p.numel()):
+            # one launch for many gradients: this one waits (still owned by the parameter) until enough bytes have
+            # gathered, the data-parallel wrapper is about to reduce its bucket, or the buffer is next read as a whole
+            if i in self._stolen_set:          # queued by an earlier micro-batch; autograd has added to it in place
+                return
+            self._stolen.append(i)
+            self._stolen_set.add(i)
+            self._stolen_bytes += g.numel() * g.element_size()
+            if self._stolen_bytes >= _LAND_FLUSH_BYTES:
+                self.flush_landing()
+        else:
             want.copy_(g)
-        p.grad = want
+            p.grad = want
+
+    def flush_landing(self):
+        """Copies every gradient that waits in its own allocation into its slice of the flat buffer — one b2_land_copy
+        launch instead of one copy per parameter — and points the parameters' .grad at the slices."""
+        if not self._stolen:
+            return
+        from . import ops
+        idx, self._stolen, self._stolen_bytes = self._stolen, [], 0
+        self._stolen_set.clear()
+        srcs, offs, keep = [], [], []
+        for i in idx:
+            p = self.params[i]
+            g, want = p.grad, self.grad_view(i)
+            if g is None or g is want or g.data_ptr() == want.data_ptr():
+                continue                       # dropped or re-pointed since it was queued
+            srcs.append(g)
+            offs.append(self.offsets[i])
+            keep.append(i)
+        ops.land_copy(srcs, self.grad, offs)
+        for i in keep:
+            self.params[i].grad = self.grad_view(i)
 
     def install_grads(self):
         """Make every parameter's .grad its slice of the flat gradient buffer, as the kernels that run over the whole
         buffer (sum of squares, all-reduce, AdamW) expect: a gradient that lives elsewhere (assigned by hand, or produced
         before the buffer existed) is copied in; a parameter WITHOUT a gradient gets a zeroed slice (it contributes
         nothing to the norm; the optimizer skips it, see AdamW._table_for)."""
+        self.flush_landing()
         moved = 0
         self.grad_view(0) if self.params else None
         for p, want in zip(self.params, self._views or ()):
@@ -120,6 +162,8 @@ class FlatBuffer:
     def zero_grad(self):
         """`optimizer.zero_grad(set_to_none=True)` (ref: ray-jobs/pytorch_llm_ray.py:273): the gradients are dropped, as
         in torch — the flat buffer is NOT cleared; each slice is overwritten when its gradient lands."""
+        self._stolen, self._stolen_bytes = [], 0
+        self._stolen_set.clear()
         for p in self.params:
             p.grad = None
         self.pending_coef = None

@@ -148,6 +148,7 @@ class _LMHeadCEFn(torch.autograd.Function):
         if need_dW and ctx.w_param is not None and W.shape == ctx.w_param.shape:
             f = flat_of(ctx.w_param)
             if f is not None:
+                f[0].flush_landing()             # (a gradient of this parameter still waiting to be copied in lands first)
                 view = f[0].grad_view(f[0]._index[id(ctx.w_param)])
                 have = ctx.w_param.grad is not None and ctx.w_param.grad.data_ptr() == view.data_ptr()
                 if ctx.w_shared or not have:

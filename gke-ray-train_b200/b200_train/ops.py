@@ -269,3 +269,19 @@ def lmhead_ce_bwd(H, W, labels, lse, gscale, row0, rows, dlogits, *, kept, dH=No
              dlogits.stride(0), int(bool(kept)), ptr(dH), 0 if dH is None else dH.stride(0), ptr(dW),
              0 if dW is None else dtype_code(dW.dtype), 0 if dW is None else dW.stride(0), int(bool(dW_accumulate)),
              ptr(db), int(bool(db_accumulate)), ptr(ws), ws_bytes, stream_ptr())
+
+
+def land_copy(srcs, dst, dst_offsets):
+    """Copies the contiguous tensors `srcs` into the flat tensor `dst` at element offsets `dst_offsets` with one launch
+    (b2_land_copy). All tensors share dst's dtype; sources must be 16-byte aligned (fresh allocations are)."""
+    import ctypes
+    n = len(srcs)
+    if n == 0:
+        return
+    require_cuda(dst, *srcs)
+    es = dst.element_size()
+    ptrs = (ctypes.c_void_p * n)(*[t.data_ptr() for t in srcs])
+    offs = (ctypes.c_size_t * n)(*[int(o) * es for o in dst_offsets])
+    sizes = (ctypes.c_size_t * n)(*[t.numel() * es for t in srcs])
+    with torch.cuda.device(dst.device):
+        call("b2_land_copy", ptrs, offs, sizes, n, ptr(dst), stream_ptr())

@@ -184,6 +184,15 @@ int b2_gemm_bf16(const void* A, int a_mn_major, long long lda, const void* B, in
  * range is split up to 6 ways into fp32 partials that a second kernel adds in a fixed order. NULL = never split. */
 size_t b2_gemm_workspace_bytes(int M, int N);
 
+/* ---- gradient landing: many gradient tensors copied into the flat gradient buffer by one launch -------------------
+ * Replaces the per-parameter bucket copies of torch's DistributedDataParallel during backward (Reducer::
+ * mark_variable_ready_dense: bucket_view.copy_(grad); wrapper installed by ray.train.torch.prepare_model, ref:
+ * ray-jobs/pytorch_llm_ray.py:230,276). srcs / dst_offsets_bytes / nbytes: HOST arrays of `count` entries — segment k is
+ * nbytes[k] bytes at device address srcs[k], copied to dst_base + dst_offsets_bytes[k]. Sources and destination offsets
+ * 16-byte aligned; sizes arbitrary; segments must not overlap. Any number of segments (112 per launch internally). */
+int b2_land_copy(const void* const* srcs, const size_t* dst_offsets_bytes, const size_t* nbytes, int count, void* dst_base,
+                 b2_stream_t stream);
+
 /* ---- input side: sliding token windows gathered on the device -------------------------------------------------
  * Replaces TextDataset.__getitem__ + DataLoader collate + the host-to-device copy of prepare_data_loader — ref:
  * ray-jobs/pytorch_llm_ray.py:107-119, 206-216. tokens: int64 [n_tokens] resident on the device; starts: int64 [B];

@@ -283,6 +283,29 @@ def test_lmhead_ce_bwd_one_call_matches_oracle_gradients(ops, N, D, V, shift_T, 
     np.testing.assert_allclose(db2.cpu().numpy(), 2 * db.cpu().numpy(), rtol=1e-5, atol=1e-8)
 
 
+# ------------------------------------------------------------------------------------------ gradient landing
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float32])
+def test_land_copy_moves_many_ragged_segments_in_one_call(ops, dtype):
+    """b2_land_copy: bit-exact copies of many separately allocated tensors into their slices of a flat buffer — sizes
+    from one element to several chunks, more segments than one launch holds, untouched gaps in between."""
+    g = torch.Generator(device="cpu").manual_seed(5)
+    sizes = [1, 7, 8, 9, 63, 64, 1000, 16384, 16385, (1 << 20) + 3, 40000] + [int(x) for x in torch.randint(1, 5000, (140,), generator=g)]
+    srcs = [torch.randn(n, generator=g).to(dev(), dtype) for n in sizes]
+    offs, off = [], 0
+    for n in sizes:
+        offs.append(off)
+        off += (n + 63) // 64 * 64 + 64            # 64-element aligned slices with a gap after each
+    flat = torch.full((off,), 7.0, dtype=dtype, device=dev())
+    ops.land_copy(srcs, flat, offs)
+    want = torch.full((off,), 7.0, dtype=dtype, device=dev())
+    for t, o in zip(srcs, offs):
+        want[o:o + t.numel()] = t
+    assert torch.equal(flat, want)
+    ops.land_copy([], flat, [])                     # nothing to do is legal
+    with pytest.raises(Exception):
+        ops.land_copy([srcs[6][1:]], flat, [0])     # a source that is not 16-byte aligned is refused, not mis-copied
+
+
 # ------------------------------------------------------------------------------------------ clip
 @pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
 @pytest.mark.parametrize("n", [1, 7, 8, 1000, 1 << 20, (1 << 22) + 13])
