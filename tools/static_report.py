@@ -4,7 +4,7 @@
 on tensor memory, TMA loads/stores, multimem, 128/256-bit global accesses). Mnemonic names follow
 /opt/skills/guides/B200_PROFILING.md.
 
-    python tools/static_report.py > profiles/r1_static_sass.txt
+    python tools/static_report.py > profiles/r2_static_sass.txt
 """
 import collections
 import os
