@@ -10,7 +10,7 @@ import csv
 import gzip
 import io
 
-OURS = ("umma_kernel", "adamw", "sumsq", "clip_coef", "ce_", "splitk", "peer_", "scale_kernel", "gather_windows", "colsum")
+OURS = ("umma_kernel", "adamw", "sumsq", "clip_coef", "ce_", "splitk", "peer_", "scale_kernel", "gather_windows", "colsum", "land_copy")
 
 
 def main():
