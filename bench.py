@@ -233,8 +233,9 @@ def f1_roofline(torch, b200, model, device, peaks, iters=5):
             # dram__bytes_read + dram__bytes_write summed over the family's launches, one `ncu --set full` capture per route
             # (profiles/r2_f1_ncu_metrics_final.json): kept route 0.89 (forward+store) + 1.59 (in-place gradient) + 1.14 (dH incl.
             # split-K reduce) + 1.09 (dW) GB; recompute route 0.10 + 0.86 + 1.14 + 1.09 GB. Algorithmic (no N*V term): 0.347 GB
-            "traffic": F1_TRAFFIC_KEPT if keep else F1_TRAFFIC_RECOMPUTE,
-            "traffic_recompute_route": F1_TRAFFIC_RECOMPUTE,
+            # (captured at the GPT-2 head, N = 8192, D = 768, V = 50 257: null for the other workloads' head shapes)
+            "traffic": (F1_TRAFFIC_KEPT if keep else F1_TRAFFIC_RECOMPUTE) if (N, D, V) == (8192, 768, 50257) else None,
+            "traffic_recompute_route": F1_TRAFFIC_RECOMPUTE if (N, D, V) == (8192, 768, 50257) else None,
             "route": "kept-logits" if keep else "recompute",
             "kernel": kernel,
             "ms": ms, "algorithmic_flops": flops, "launches": parts, "dlogits_recompute_route": other,
