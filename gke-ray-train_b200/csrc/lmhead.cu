@@ -87,6 +87,7 @@ struct Params {
   const float* lse; const float* gscale; __nv_bfloat16* dlogits; long long ldd;
   int store_wide;                    // storing modes: 1 = one [32 x 64] TMA store per two chunks, 0 = one [32 x 32] per chunk
   int debug_store;                   // measurement aid (B2_DEBUG_STORE): 1 = stage the tile but issue no TMA store, 2 = drop it
+  int store_evict_normal;            // storing modes: 0 = evict-first hint on the tile stores (default), 1 = normal policy
   int store_direct;                  // storing modes: 1 = each thread writes its 64-byte row segment straight to global memory
                                      // (no shared-memory staging, no TMA store); needs p.dlogits / p.ldd
 };
@@ -260,7 +261,9 @@ umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
     int as = 0; uint32_t aphase = 0;
     uint32_t store_seq = 0;                         // storing modes: staging box toggle
     const bool lane_elect = elect_one();            // the lane that issues this warp's TMA stores / barrier arrivals
-    const uint64_t store_policy = l2_policy_evict_first();
+    // written once, read later by other kernels: by default the stores carry an evict-first hint so they do not displace
+    // the W tiles being re-read from L2 (p.store_evict_normal: plain policy, A/B aid B2_STORE_POLICY=normal)
+    const uint64_t store_policy = p.store_evict_normal ? l2_policy_evict_normal() : l2_policy_evict_first();
     for (int u = cid; u < num_units; u += ncl) {
       const Unit t = decode_unit(p, u);
       const int s = t.s, nb0 = t.nb0, nb1 = t.nb1;
@@ -559,10 +562,13 @@ __global__ void __launch_bounds__(256) ce_dlogits_inplace_kernel(__nv_bfloat16* 
                                                                  const long long* __restrict__ labels, long long row0,
                                                                  long long rows, int V, int shift_T, long long ignore_index,
                                                                  const float* __restrict__ lse,
-                                                                 const float* __restrict__ gscale) {
+                                                                 const float* __restrict__ gscale, int reverse) {
   const int nvec = (V + 7) >> 3;
   const float g = __ldg(gscale);
-  for (long long row = blockIdx.y; row < rows; row += gridDim.y) {
+  for (long long r = blockIdx.y; r < rows; r += gridDim.y) {
+    // LAST rows first (blocks are scheduled in increasing blockIdx.y): the forward that left these logits wrote its last
+    // rows last, so they are the ones still in L2; and the rows written last HERE are the first ones the dH GEMM reads
+    const long long row = reverse ? rows - 1 - r : r;
     const long long i = row0 + row;
     long long y = (shift_T <= 0) ? labels[i] : (((i % shift_T) + 1 < shift_T) ? labels[i + 1] : ignore_index);
     const bool valid = (y != ignore_index) && y >= 0 && y < V;
@@ -703,6 +709,15 @@ int store_direct_env() {
 // direct stores need a 32-byte aligned buffer whose row pitch is a multiple of 16 elements
 bool store_direct_ok(const void* ptr, long long pitch) {
   return store_direct_env() == 1 && pitch % 16 == 0 && b2_aligned(ptr, 32);
+}
+int store_evict_normal() {
+  static const int v = [] { const char* e = getenv("B2_STORE_POLICY"); return (e != nullptr && e[0] == 'n') ? 1 : 0; }();
+  return v;
+}
+// B2_TRANSFORM_REVERSE=0: the in-place soft-max gradient walks the rows front to back (A/B aid; default: back to front)
+int transform_reverse() {
+  static const int v = [] { const char* e = getenv("B2_TRANSFORM_REVERSE"); return e == nullptr ? 1 : (e[0] != '0'); }();
+  return v;
 }
 bool store_wide() {
   static const bool wide = [] { const char* e = getenv("B2_STORE_BOX"); return e == nullptr ? true : atoi(e) == 64; }();
@@ -901,7 +916,7 @@ static int lmhead_ce_fwd_impl(const void* H, long long ldh, const void* W, long 
     } else {
       CUtensorMap td;
       if ((rc = make_store_tmap(&td, logits_out, V, N, ldl, "b2_lmhead_ce_fwd_keep logits")) != B2_OK) return rc;
-      p.store_wide = store_wide(); p.debug_store = debug_store();
+      p.store_wide = store_wide(); p.debug_store = debug_store(); p.store_evict_normal = store_evict_normal();
       p.dlogits = static_cast<__nv_bfloat16*>(logits_out); p.ldd = ldl; p.store_direct = store_direct_ok(logits_out, ldl);
       if ((rc = launch<MODE_CE_FWD_KEEP, 0, 0>(pair, ta, tb, td, p, stream)) != B2_OK) return rc;
     }
@@ -945,7 +960,7 @@ extern "C" int b2_ce_dlogits_inplace(void* logits, long long ldl, const long lon
   const unsigned gx = (unsigned)((nvec + 256 * 4 - 1) / (256 * 4));
   const unsigned gy = (unsigned)(rows < 65535 ? rows : 65535);
   ce_dlogits_inplace_kernel<<<dim3(gx, gy), 256, 0, stream>>>(static_cast<__nv_bfloat16*>(logits), ldl, labels, row0, rows,
-                                                             V, shift_T, ignore_index, lse, gscale_dev);
+                                                             V, shift_T, ignore_index, lse, gscale_dev, transform_reverse());
   B2_CHECK_CUDA(cudaGetLastError());
   return B2_OK;
 }
@@ -975,6 +990,7 @@ extern "C" int b2_lmhead_ce_bwd_dlogits(const void* H, long long ldh, const void
   CUtensorMap td;
   if ((rc = make_store_tmap(&td, dlogits, V, rows, ldd, "b2_lmhead_ce_bwd_dlogits dlogits")) != B2_OK) return rc;
   p.store_wide = store_wide(); p.debug_store = debug_store(); p.store_direct = store_direct_ok(dlogits, ldd);
+  p.store_evict_normal = store_evict_normal();
   return launch<MODE_CE_BWD, 0, 0>(pair, ta, tb, td, p, stream);
 }
 
