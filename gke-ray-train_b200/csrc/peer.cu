@@ -179,7 +179,7 @@ template <> struct PeerVec<B2_BF16> {
 
 // vectors [v0, v1) of 16 bytes belong to this rank
 template <int DT, int WORLD, bool SCATTER_ONLY>
-__global__ void __launch_bounds__(512) peer_allreduce_kernel(const __grid_constant__ PeerPtrs pp, int rank, size_t v0,
+__global__ void __launch_bounds__(512, 2) peer_allreduce_kernel(const __grid_constant__ PeerPtrs pp, int rank, size_t v0,
                                                              size_t v1, float scale, uint32_t epoch, int want_sumsq,
                                                              float* sumsq_out) {
   using V = PeerVec<DT>;
@@ -187,33 +187,48 @@ __global__ void __launch_bounds__(512) peer_allreduce_kernel(const __grid_consta
   start_barrier(pp, WORLD, rank, epoch);
 
   float ss = 0.f;
+  // Loads in flight per thread: WORLD per vector. With few ranks that is too little to cover the NVLink round trip, so
+  // small worlds take several vectors per iteration (8 loads in flight for W <= 4). Element order, and with it every
+  // result bit and the order of the sum of squares, is unchanged.
+  constexpr int U = WORLD <= 2 ? 4 : (WORLD <= 4 ? 2 : 1);
   const size_t stride = (size_t)gridDim.x * blockDim.x;
-  for (size_t i = v0 + (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < v1; i += stride) {
-    uint4 in[WORLD];
+  for (size_t i0 = v0 + (size_t)blockIdx.x * blockDim.x + threadIdx.x; i0 < v1; i0 += stride * U) {
+    uint4 in[U][WORLD];
 #pragma unroll
-    for (int k = 0; k < WORLD; ++k) in[k] = ld_peer(static_cast<const uint4*>(pp.buf[k]) + i);   // all loads in flight
-    float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+    for (int u = 0; u < U; ++u) {
+      const size_t i = i0 + (size_t)u * stride;
+      if (i < v1) {
 #pragma unroll
-    for (int k = 0; k < WORLD; ++k) {                                                             // fixed rank order
-      float x[8];
-      V::unpack(in[k], x);
-#pragma unroll
-      for (int e = 0; e < 8; ++e) acc[e] += x[e];
+        for (int k = 0; k < WORLD; ++k) in[u][k] = ld_peer(static_cast<const uint4*>(pp.buf[k]) + i);   // all loads in flight
+      }
     }
 #pragma unroll
-    for (int e = 0; e < 8; ++e) acc[e] *= scale;
-    const uint4 out = V::pack(acc);
-    if (want_sumsq) {
-      float y[8];
-      V::unpack(out, y);                                   // the rounded values, as clip_grad_norm_ would read them
+    for (int u = 0; u < U; ++u) {
+      const size_t i = i0 + (size_t)u * stride;
+      if (i >= v1) break;
+      float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
 #pragma unroll
-      for (int e = 0; e < 8; ++e) ss = fmaf(y[e], y[e], ss);
-    }
-    if (SCATTER_ONLY) {
-      st_peer(static_cast<uint4*>(pp.buf[rank]) + i, out);
-    } else {
+      for (int k = 0; k < WORLD; ++k) {                                                           // fixed rank order
+        float x[8];
+        V::unpack(in[u][k], x);
 #pragma unroll
-      for (int k = 0; k < WORLD; ++k) st_peer(static_cast<uint4*>(pp.buf[k]) + i, out);
+        for (int e = 0; e < 8; ++e) acc[e] += x[e];
+      }
+#pragma unroll
+      for (int e = 0; e < 8; ++e) acc[e] *= scale;
+      const uint4 out = V::pack(acc);
+      if (want_sumsq) {
+        float y[8];
+        V::unpack(out, y);                                 // the rounded values, as clip_grad_norm_ would read them
+#pragma unroll
+        for (int e = 0; e < 8; ++e) ss = fmaf(y[e], y[e], ss);
+      }
+      if (SCATTER_ONLY) {
+        st_peer(static_cast<uint4*>(pp.buf[rank]) + i, out);
+      } else {
+#pragma unroll
+        for (int k = 0; k < WORLD; ++k) st_peer(static_cast<uint4*>(pp.buf[k]) + i, out);
+      }
     }
   }
 
