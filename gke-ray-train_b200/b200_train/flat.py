@@ -95,8 +95,7 @@ class FlatBuffer:
         if g is None or g.data_ptr() == want.data_ptr():
             p.grad = want
             return
-        if (g.is_cuda and g.dtype == self.dtype and g.is_contiguous() and g.data_ptr() % 16 == 0
-                and g.numel() == p.numel()):
+        if self._can_queue(g, p):
             # one launch for many gradients: this one waits (still owned by the parameter) until enough bytes have
             # gathered, the data-parallel wrapper is about to reduce its bucket, or the buffer is next read as a whole
             if i in self._stolen_set:          # queued by an earlier micro-batch; autograd has added to it in place
@@ -109,6 +108,11 @@ class FlatBuffer:
         else:
             want.copy_(g)
             p.grad = want
+
+    def _can_queue(self, g, p):
+        """A gradient the gather kernel can take: on the device, the buffer's dtype, contiguous, 16-byte aligned."""
+        return (g.is_cuda and g.dtype == self.dtype and g.is_contiguous() and g.data_ptr() % 16 == 0
+                and g.numel() == p.numel())
 
     def flush_landing(self):
         """Copies every gradient that waits in its own allocation into its slice of the flat buffer — one b2_land_copy

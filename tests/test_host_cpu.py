@@ -52,6 +52,56 @@ def test_flatten_keeps_parameters_and_values():
     assert buffers_of(list(m.parameters()))[0] == bufs
 
 
+def test_gradient_landing_queue_logic(monkeypatch):
+    """The bookkeeping around b2_land_copy, on the CPU with the kernel replaced by a plain copy loop: gradients wait in
+    their own allocations until the byte threshold, a flush moves them all and re-points .grad, a second micro-batch adds
+    into a gradient that still waits (queued once), zero_grad() forgets the queue, install_grads() flushes."""
+    from b200_train import flat as F
+    from b200_train import ops
+    calls = []
+
+    def fake_land_copy(srcs, dst, offs):
+        calls.append(len(srcs))
+        for t, o in zip(srcs, offs):
+            dst[o:o + t.numel()] = t.reshape(-1)
+
+    monkeypatch.setattr(ops, "land_copy", fake_land_copy)
+    monkeypatch.setattr(F, "_LAND_FLUSH_BYTES", 1 << 30)          # nothing flushes by size
+    torch.manual_seed(0)
+    m = nn.Sequential(nn.Linear(5, 7), nn.LayerNorm(7), nn.Linear(7, 3))
+    buf = F.flatten_params(list(m.parameters()))[0]
+    monkeypatch.setattr(buf, "_can_queue", lambda g, p: True)
+    x = torch.randn(4, 5)
+    ref = [g.clone() for g in torch.autograd.grad(m(x).sum(), list(m.parameters()))]
+    buf.grad.fill_(9.0)
+    m(x).sum().backward()
+    assert not calls and sorted(buf._stolen) == list(range(len(buf.params)))      # all of them wait, in their own memory
+    assert all(p.grad is not buf.grad_view(i) and torch.equal(p.grad, ref[i]) for i, p in enumerate(buf.params))
+    m(x).sum().backward()                                         # second micro-batch: in-place adds, queued only once
+    assert len(buf._stolen) == len(set(buf._stolen)) == len(buf.params)
+    buf.install_grads()                                           # what clip / step / the bucket launch do first
+    assert calls == [len(buf.params)] and not buf._stolen
+    for i, p in enumerate(buf.params):
+        assert p.grad is buf.grad_view(i) and torch.allclose(p.grad, 2 * ref[i])
+    # a small threshold flushes while backward is still running
+    monkeypatch.setattr(F, "_LAND_FLUSH_BYTES", 100)
+    buf.zero_grad()
+    del calls[:]
+    m(x).sum().backward()
+    assert len(calls) >= 2
+    buf.install_grads()
+    assert all(torch.equal(p.grad, r) for p, r in zip(buf.params, ref))
+    # gradients dropped while some still wait: nothing of them may be copied later
+    monkeypatch.setattr(F, "_LAND_FLUSH_BYTES", 1 << 30)
+    buf.zero_grad()
+    m(x).sum().backward()
+    buf.zero_grad()
+    del calls[:]
+    assert not buf._stolen and all(p.grad is None for p in buf.params)
+    buf.flush_landing()
+    assert not calls
+
+
 def test_tied_weights_are_flattened_once():
     from b200_train.flat import flatten_params
     emb = nn.Embedding(11, 4)
