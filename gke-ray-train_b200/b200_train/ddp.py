@@ -339,6 +339,8 @@ class DistributedDataParallel(nn.Module):
     def forward_prepare(self):
         """Forward-side bookkeeping (stale reductions forgotten). forward() calls it; call it yourself only when you
         drive `self.module` piecewise (e.g. its feature extractor + a fused loss)."""
+        if not torch.is_grad_enabled():
+            return                  # an evaluation pass between backward and clip must not forget the reduction's Σg²
         for buf in self.flat_buffers:
             buf.reduced_sumsq = None
 
