@@ -129,9 +129,12 @@ def configs0_gloo_baseline(TR):
     than the headline workload, so it is reported NEXT TO the GPT-2 sample, not as `value`."""
     out = {"host_cores": os.cpu_count(), "workers": 2, "backend": "gloo", "launcher": "b200_train.train.TorchTrainer (ray is not installed)"}
     # under torchrun this process carries RANK / WORLD_SIZE of the GPU job: the trainer must start its own two workers
-    saved = {k: os.environ.pop(k) for k in ("RANK", "LOCAL_RANK", "WORLD_SIZE", "MASTER_ADDR", "MASTER_PORT",
-                                            "LOCAL_WORLD_SIZE", "GROUP_RANK", "ROLE_RANK", "TORCHELASTIC_RUN_ID")
-             if k in os.environ}
+    # (TORCHELASTIC_USE_AGENT_STORE in particular: with it set, the workers' env:// rendezvous would wait for the torchrun
+    # agent's store on a port nobody serves; OMP_NUM_THREADS=1 is torchrun's default and would cap the workers' threads)
+    drop = [k for k in os.environ if k.startswith("TORCHELASTIC_") or k in (
+        "RANK", "LOCAL_RANK", "WORLD_SIZE", "MASTER_ADDR", "MASTER_PORT", "LOCAL_WORLD_SIZE", "GROUP_RANK", "ROLE_RANK",
+        "ROLE_NAME", "ROLE_WORLD_SIZE", "GROUP_WORLD_SIZE", "OMP_NUM_THREADS", "TORCH_NCCL_ASYNC_ERROR_HANDLING")]
+    saved = {k: os.environ.pop(k) for k in drop}
     try:
         _configs0_runs(TR, out)
     finally:

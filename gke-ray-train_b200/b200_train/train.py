@@ -22,6 +22,7 @@ import os
 import shutil
 import socket
 import tempfile
+import time as _time
 import types
 from dataclasses import dataclass, field
 from typing import Any, Callable, Dict, Optional
@@ -344,8 +345,15 @@ class TorchTrainer:
         # the OOM killer, a segfault in native code, a failed import in the spawned interpreter): the queue is polled
         # while the process context is checked; ProcessContext.join raises as soon as any worker has failed.
         results = {}
+        deadline = _time.monotonic() + float(self.torch_config.timeout_s or 1800)
         try:
             while len(results) < world:
+                if _time.monotonic() > deadline:
+                    for pr in procs.processes:
+                        if pr.is_alive():
+                            pr.terminate()
+                    return Result(metrics=None, path=storage_dir,
+                                  error=TimeoutError(f"workers did not report within {self.torch_config.timeout_s} s"))
                 if not queue.empty():
                     rank, reports, err = queue.get()
                     results[rank] = (reports, err)

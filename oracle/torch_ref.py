@@ -131,7 +131,7 @@ def cpu_gloo_small_gpt_baseline(steps=5, warmup=2, world=2, threads=None):
     threads = threads or max(1, (os.cpu_count() or 2) // world)
     res = TorchTrainer(small_gpt_gloo_loop, train_loop_config={"steps": steps, "warmup": warmup, "threads": threads},
                        scaling_config=ScalingConfig(num_workers=world, use_gpu=False),
-                       torch_config=TorchConfig(backend="gloo")).fit()
+                       torch_config=TorchConfig(backend="gloo", timeout_s=240)).fit()
     if res.error is not None or not res.metrics:
         raise RuntimeError(f"CPU gloo baseline failed: {res.error!r}")
     sec = res.metrics["sec_per_step"]

@@ -358,3 +358,25 @@ def test_hf_cosine_schedule_drives_our_param_groups_like_torchs():
         lrs[name] = seq
     assert lrs["ours"] == lrs["torch"]
     assert lrs["ours"][0] == [0.0, 0.0] and max(v[0] for v in lrs["ours"]) == pytest.approx(2e-4)
+
+
+def test_reference_arm_scrubs_the_torchrun_environment(monkeypatch):
+    """bench.py's CPU legs start their own two gloo workers; under torchrun the parent's RANK / WORLD_SIZE / TORCHELASTIC_*
+    variables (TORCHELASTIC_USE_AGENT_STORE makes an env:// rendezvous wait for the agent's store) must not leak into them,
+    and must be back afterwards."""
+    import bench
+    for k, v in {"RANK": "0", "WORLD_SIZE": "2", "LOCAL_RANK": "0", "MASTER_ADDR": "127.0.0.1", "MASTER_PORT": "29999",
+                 "TORCHELASTIC_USE_AGENT_STORE": "True", "TORCHELASTIC_RUN_ID": "x", "OMP_NUM_THREADS": "1"}.items():
+        monkeypatch.setenv(k, v)
+    seen = []
+
+    class FakeTR:
+        @staticmethod
+        def cpu_gloo_small_gpt_baseline(steps, warmup, world, threads):
+            seen.append({k for k in os.environ if k.startswith("TORCHELASTIC_") or k in ("RANK", "WORLD_SIZE", "MASTER_PORT", "OMP_NUM_THREADS")})
+            return dict(tokens_per_s=1.0, ms_per_step=1.0, sample="fake")
+
+    out = bench.configs0_gloo_baseline(FakeTR)
+    assert seen == [set(), set()]
+    assert out["threads_1_per_worker"]["value"] == 1.0 and out["workers"] == 2
+    assert os.environ["TORCHELASTIC_USE_AGENT_STORE"] == "True" and os.environ["RANK"] == "0"
