@@ -100,6 +100,7 @@ def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
+    os.environ.pop("OMP_NUM_THREADS", None)       # torchrun sets it to 1; this arm uses every host thread it can
     import torch
     from oracle import torch_ref as TR
     torch.set_num_threads(os.cpu_count() or 1)
